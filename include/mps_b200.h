@@ -1,0 +1,191 @@
+/* mps_b200.h — C ABI of the B200-native MPS time step (libmps_b200.so).
+ *
+ * This is the drop-in boundary: it sits INSIDE the reference's `MPS` class, underneath its
+ * unchanged public members (reference src/mps.hpp:61-70), and replaces the private phase
+ * functions of reference src/mps.cpp. Plain pointers and sizes only; no C++/torch types.
+ * All arrays are host pointers unless a function says "device". Every function returns 0 on
+ * success and a negative mpsb_status otherwise; it never throws. There is NO CPU fallback:
+ * without a CUDA device every compute entry point fails with MPSB_ERR_CUDA.
+ *
+ * Particle arrays are SoA, indexed by particle id (the reference assumes id == index,
+ * src/mps.cpp:599-617, src/bucket.cpp:36-50). Vectors are packed xyz (3 doubles per particle).
+ */
+#ifndef MPS_B200_H
+#define MPS_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Values of reference `enum class ParticleType` (src/particle.hpp:5) */
+enum { MPSB_GHOST = -1, MPSB_FLUID = 0, MPSB_WALL = 1, MPSB_DUMMY_WALL = 2 };
+/* Values of reference `enum class BoundaryCondition` (src/particle.hpp:19) */
+enum { MPSB_BC_IGNORED = 0, MPSB_BC_SURFACE = 1, MPSB_BC_INNER = 2 };
+
+typedef enum mpsb_status {
+    MPSB_OK               = 0,
+    MPSB_ERR_ARG          = -1, /* bad argument */
+    MPSB_ERR_CUDA         = -2, /* CUDA runtime failure or no device (sticky on the handle) */
+    MPSB_ERR_CAPACITY     = -3, /* neighbour-list / candidate capacity exceeded */
+    MPSB_ERR_OUT_OF_GRID  = -4, /* a non-ghost particle left the padded cell grid (reference would index OOB, SURVEY B-8) */
+    MPSB_ERR_COMM         = -5  /* multi-GPU exchange failure */
+} mpsb_status;
+
+/* Flattened reference `Settings` (src/settings.hpp:35-86) plus the three `RefValues`
+ * (src/mps.hpp:10-20, src/mps.cpp:132-163), which the host computes with the reference's
+ * loop order so n0/lambda are bit-identical. */
+typedef struct mpsb_settings {
+    int32_t dim;                      /* settings.dim */
+    int32_t quasi_compressibility_on; /* settings.quasiCompressibility.on */
+    int32_t higher_order_source_on;   /* settings.higherOrderSourceTerm.on */
+    int32_t reserved0;
+    double particle_distance;         /* l0 */
+    double dt;
+    double cfl_condition;
+    double domain_min[3];
+    double domain_max[3];
+    double density;
+    double kinematic_viscosity;
+    double gravity[3];
+    double re_pressure;               /* effectiveRadius.pressure (already multiplied by l0) */
+    double re_viscosity;
+    double re_surface;
+    double re_max;
+    double surface_threshold;         /* thresholdForSurfaceDetection (beta) */
+    double compressibility;           /* quasiCompressibility.compressibility (alpha) */
+    double higher_order_gamma;
+    double relaxation_coefficient;    /* relaxationCoefficientForPressure */
+    double collision_distance;        /* already multiplied by l0 */
+    double restitution;
+    double n0_pressure, lambda_pressure;
+    double n0_viscosity, lambda_viscosity;
+    double n0_surface, lambda_surface;
+} mpsb_settings;
+
+/* Per-step report. Times are CUDA-event milliseconds on the handle's stream. */
+typedef struct mpsb_step_stats {
+    double courant;          /* return value of reference getCourantNumber (src/mps.cpp:547-571) */
+    double cg_rel_residual;  /* sqrt(|r|^2/|b|^2) at exit, Eigen's error() */
+    double ms_total;
+    double ms_neighbors;     /* all neighbour-list builds of the step */
+    double ms_explicit;      /* gravity + viscosity + move */
+    double ms_collision;
+    double ms_assemble;      /* flags, source term, matrix, Dirichlet connectivity */
+    double ms_solve;         /* the PCG solve (reference solvePoissonEquation) */
+    double ms_correct;       /* clamp, minimum pressure, gradient, correction, Courant */
+    int32_t cg_iterations;
+    int32_t n_active;        /* non-ghost particles at the end of the step */
+    int32_t n_inner;         /* PPE unknowns (BoundaryCondition::Inner) */
+    int32_t n_surface;
+    int32_t nnz;             /* stored PPE entries incl. diagonal */
+    int32_t n_ghosted;       /* particles turned Ghost in this step (debugLogCount += ) */
+    int32_t n_unconnected;   /* Inner particles with no Dirichlet connection (debugLogCount += ) */
+    int32_t n_collisions;    /* collision candidates replayed (dist < collisionDistance) */
+    int32_t max_neighbors;   /* longest neighbour list seen in the step */
+    int32_t courant_exceeds_cfl; /* 1 if courant > cfl_condition (debugLogCount += ) */
+    int32_t reserved[2];
+} mpsb_step_stats;
+
+typedef struct mpsb_handle mpsb_handle;
+
+/* Phases for mpsb_run_phase (parity tests drive the step piecewise, teacher-forced).
+ * Each names the reference function(s) it replaces. */
+typedef enum mpsb_phase {
+    MPSB_PH_NEIGHBORS       = 0, /* setNeighbors            src/mps.cpp:585-619 + bucket.cpp:24-51 */
+    MPSB_PH_EXPLICIT        = 1, /* calcGravity+calcViscosity+moveParticles   :165-215 */
+    MPSB_PH_COLLISION       = 2, /* collision               :217-250 */
+    MPSB_PH_FLAGS_SOURCE    = 3, /* setBoundaryCondition+setSourceTerm        :262-320 */
+    MPSB_PH_MATRIX          = 4, /* setMatrix               :322-360 */
+    MPSB_PH_DIRICHLET       = 5, /* ensureDirichletBoundaryConnection         :362-415 */
+    MPSB_PH_SOLVE           = 6, /* solvePoissonEquation    :417-470 */
+    MPSB_PH_PRESSURE_POST   = 7, /* removeNegativePressure+setMinimumPressure :472-503 */
+    MPSB_PH_GRADIENT_MOVE   = 8, /* calcPressureGradient+moveParticlesWithPressureGradient :505-545 */
+    MPSB_PH_NUMBER_DENSITY  = 9, /* setNumberDensity (includes its own setNeighbors) :627-641 */
+    MPSB_PH_COURANT         = 10 /* getCourantNumber        :547-571 */
+} mpsb_phase;
+
+/* Field mask bits for upload/download. */
+enum {
+    MPSB_F_TYPE     = 1 << 0, /* int32[n]   */
+    MPSB_F_POSITION = 1 << 1, /* double[3n] */
+    MPSB_F_VELOCITY = 1 << 2, /* double[3n] */
+    MPSB_F_ACCEL    = 1 << 3, /* double[3n] */
+    MPSB_F_PRESSURE = 1 << 4, /* double[n]  */
+    MPSB_F_MIN_PRESSURE = 1 << 5, /* double[n] */
+    MPSB_F_NUMBER_DENSITY_RATIO = 1 << 6, /* double[n] */
+    MPSB_F_BOUNDARY_CONDITION   = 1 << 7, /* int32[n] */
+    MPSB_F_ALL = 0xFF
+};
+
+typedef struct mpsb_fields {
+    int32_t* type;
+    double* position;
+    double* velocity;
+    double* acceleration;
+    double* pressure;
+    double* minimum_pressure;
+    double* number_density_ratio;
+    int32_t* boundary_condition;
+} mpsb_fields;
+
+/* --- lifetime ------------------------------------------------------------------------- */
+
+/* Replaces MPS::loadInitialState's resize/Bucket construction (src/mps.cpp:96-104): creates the
+ * device state for n particles (id == index) on CUDA device `device` and uploads type, position,
+ * velocity. Pressure, min pressure, ratio start at 0 and boundary condition at Ignored
+ * (the reference leaves them uninitialised, SURVEY B-1). Does NOT run setNumberDensity —
+ * call mpsb_run_phase(MPSB_PH_NUMBER_DENSITY) as loadInitialState does (:106). */
+int mpsb_create(const mpsb_settings* settings, int64_t n, const int32_t* type,
+                const double* position, const double* velocity, int device, mpsb_handle** out);
+int mpsb_destroy(mpsb_handle* h);
+/* Last error text for the handle (or for a failed mpsb_create when h == NULL). */
+const char* mpsb_last_error(const mpsb_handle* h);
+/* Library identification: "mps_b200 <version> sm_100a". */
+const char* mpsb_version(void);
+
+/* --- the hot path --------------------------------------------------------------------- */
+
+/* Replaces MPS::stepForward (src/mps.cpp:111-130). `want_number_density` = isTimeToExport ||
+ * higherOrderSourceTerm.on (:125-127). Synchronises the stream before returning. */
+int mpsb_step(mpsb_handle* h, int want_number_density, mpsb_step_stats* stats);
+/* Run one phase of the step on the current device state (tests / teacher forcing). */
+int mpsb_run_phase(mpsb_handle* h, int phase, mpsb_step_stats* stats);
+
+/* --- state transfer (host mirror of `std::vector<Particle>`, src/particle.hpp:21-46) ----- */
+int mpsb_upload(mpsb_handle* h, uint32_t field_mask, const mpsb_fields* src);
+int mpsb_download(mpsb_handle* h, uint32_t field_mask, const mpsb_fields* dst);
+int64_t mpsb_num_particles(const mpsb_handle* h);
+
+/* --- inspection (parity tests) -------------------------------------------------------------
+ * Neighbour lists of the last build as CSR by particle id, entries in the reference's order
+ * (src/mps.cpp:599-617). Call with ids == NULL to get only row_start (n+1 entries) and size. */
+int mpsb_get_neighbors(mpsb_handle* h, int64_t* row_start, int32_t* ids, double* dist,
+                       int64_t capacity, int64_t* total);
+/* The PPE of the last MATRIX/DIRICHLET phase as CSR over particle ids (n rows, empty rows for
+ * non-Inner particles like the reference's N x N matrix, src/mps.cpp:99-100), columns ascending
+ * within a row as after Eigen setFromTriplets, plus the source term. */
+int mpsb_get_ppe(mpsb_handle* h, int64_t* row_start, int32_t* col, double* val, double* rhs,
+                 int64_t capacity, int64_t* nnz);
+/* Ids of particles behind the last step's debug-log events (src/mps.cpp:405-410, 655-663).
+ * kind 0 = ghosted (xyz = position at the time, 3 doubles each), 1 = Dirichlet-unconnected. */
+int mpsb_events(mpsb_handle* h, int kind, int32_t* ids, double* xyz, int capacity, int* count);
+
+/* --- multi-GPU (one process per GPU; slab/row partition) -------------------------------------
+ * Attach an exchange group before the first step. `nccl_unique_id` is the 128-byte ncclUniqueId
+ * produced on rank 0 and distributed by the host (torch.distributed / a launcher). */
+int mpsb_comm_unique_id(void* out128);
+int mpsb_attach_comm(mpsb_handle* h, int rank, int world_size, const void* nccl_unique_id128);
+
+/* --- device-resident entry points (bench: inputs already in HBM) ------------------------------
+ * Same as mpsb_upload for position/velocity/type but from DEVICE pointers on the handle's device. */
+int mpsb_upload_device(mpsb_handle* h, const int32_t* d_type, const double* d_position,
+                       const double* d_velocity);
+/* Counters since create: kernel launches issued by this library on this handle. */
+int64_t mpsb_launch_count(const mpsb_handle* h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MPS_B200_H */
