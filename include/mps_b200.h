@@ -182,6 +182,9 @@ int mpsb_attach_comm(mpsb_handle* h, int rank, int world_size, const void* nccl_
  * Same as mpsb_upload for position/velocity/type but from DEVICE pointers on the handle's device. */
 int mpsb_upload_device(mpsb_handle* h, const int32_t* d_type, const double* d_position,
                        const double* d_velocity);
+/* Run all subsequent work of this handle on the caller's CUDA stream (a cudaStream_t passed as
+ * void*; NULL restores the handle's own stream), so the host can bracket steps with its own events. */
+int mpsb_set_stream(mpsb_handle* h, void* cuda_stream);
 /* Counters since create: kernel launches issued by this library on this handle. */
 int64_t mpsb_launch_count(const mpsb_handle* h);
 

@@ -1,0 +1,228 @@
+// k_cells.cu — cell-list (bucket) construction: particle -> cell key, stable LSD radix sort of
+// (key, id), cell start/end ranges, and the HOME <-> SORTED permutation of the particle state.
+//
+// Replaces reference Bucket::storeParticles (src/bucket.cpp:24-51): the reference threads every
+// cell's particles on a linked list in id order; here a STABLE sort by cell key starting from id
+// order gives every cell as one contiguous range of the sorted arrays with ids ascending inside
+// it, i.e. the same traversal order. Ghosts get the maximum key and sink to the tail
+// (the reference skips them, bucket.cpp:37-38).
+#include "mpsb_internal.cuh"
+
+namespace {
+
+constexpr int SORT_THREADS = 256;
+constexpr int SORT_ITEMS   = 8;
+constexpr int SORT_TILE    = SORT_THREADS * SORT_ITEMS;
+constexpr int RADIX        = 256;
+
+// Cell key from the HOME position, by particle id. ix = (int)((x - xmin)/len) + 1 with a true
+// division and C truncation (src/bucket.cpp:40-43). A non-ghost particle whose cell would make the
+// reference's 27-cell scan index outside its arrays raises the out-of-grid flag (SURVEY B-8).
+__global__ void key_kernel(Params P) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P.N) return;
+    unsigned key = MPSB_GHOST_KEY;
+    if (P.H.type[i] != MPSB_GHOST) {
+        double len = P.s.re_max;
+        int ix = (int) ((P.H.pos[3 * i + 0] - P.s.domain_min[0]) / len) + 1;
+        int iy = (int) ((P.H.pos[3 * i + 1] - P.s.domain_min[1]) / len) + 1;
+        int iz = (int) ((P.H.pos[3 * i + 2] - P.s.domain_min[2]) / len) + 1;
+        bool bad = ix < 1 || ix > P.numX - 2 || iy < 1 || iy > P.numY - 2 || iz < 1 || iz > P.numZ - 2;
+        if (bad) {
+            atomicOr(&P.stats->error_flags, 2);
+            ix = min(max(ix, 0), P.numX - 1);
+            iy = min(max(iy, 0), P.numY - 1);
+            iz = min(max(iz, 0), P.numZ - 1);
+        }
+        key = (unsigned) (ix + iy * P.numX + iz * P.numX * P.numY);
+    }
+    P.key[i] = key;
+    P.val[i] = i;
+}
+
+// Ghost keys map to digit 255 in every pass so they stay at the tail for any number of passes.
+__device__ __forceinline__ unsigned digit_of(unsigned key, int shift) { return (key >> shift) & (RADIX - 1); }
+
+// Pass 1 of a radix pass: per-tile digit histogram, stored digit-major: hist[d * numTiles + tile].
+__global__ void radix_hist_kernel(const unsigned* __restrict__ key, int n, int shift, int numTiles,
+                                  int* __restrict__ hist) {
+    __shared__ int sh[RADIX];
+    sh[threadIdx.x] = 0;
+    __syncthreads();
+    int base = blockIdx.x * SORT_TILE;
+#pragma unroll
+    for (int it = 0; it < SORT_ITEMS; it++) {
+        int i = base + it * SORT_THREADS + threadIdx.x;
+        if (i < n) atomicAdd(&sh[digit_of(key[i], shift)], 1);
+    }
+    __syncthreads();
+    hist[threadIdx.x * numTiles + blockIdx.x] = sh[threadIdx.x];
+}
+
+// Exclusive scan of a moderate-size int array by one CTA (running carry over 4096-element chunks).
+__global__ void exclusive_scan_kernel(int* __restrict__ data, int n) {
+    constexpr int T = 1024, IT = 4;
+    __shared__ int warp_sums[32];
+    __shared__ int carry_sh;
+    if (threadIdx.x == 0) carry_sh = 0;
+    __syncthreads();
+    int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int base = 0; base < n; base += T * IT) {
+        int idx = base + threadIdx.x * IT;
+        int v[IT], sum = 0;
+#pragma unroll
+        for (int k = 0; k < IT; k++) {
+            v[k] = (idx + k < n) ? data[idx + k] : 0;
+            sum += v[k];
+        }
+        int incl = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        if (lane == 31) warp_sums[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+            int ws = warp_sums[lane], wi = ws;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                int t = __shfl_up_sync(0xffffffffu, wi, o);
+                if (lane >= o) wi += t;
+            }
+            warp_sums[lane] = wi - ws; // exclusive warp offsets
+        }
+        __syncthreads();
+        int carry = carry_sh;
+        int excl  = carry + warp_sums[warp] + (incl - sum);
+#pragma unroll
+        for (int k = 0; k < IT; k++) {
+            if (idx + k < n) data[idx + k] = excl;
+            excl += v[k];
+        }
+        __syncthreads();
+        if (threadIdx.x == T - 1) carry_sh = excl; // last thread holds the chunk total + carry
+        __syncthreads();
+    }
+}
+
+// Pass 2 of a radix pass: stable scatter. The tile is consumed 256 elements at a time in index
+// order; inside each group a warp ranks equal digits with __match_any_sync (lane order = index
+// order), warps are prefix-summed per digit, and a per-digit running offset carries between groups.
+__global__ void radix_scatter_kernel(const unsigned* __restrict__ key_in, const int* __restrict__ val_in,
+                                     unsigned* __restrict__ key_out, int* __restrict__ val_out, int n, int shift,
+                                     int numTiles, const int* __restrict__ hist) {
+    constexpr int WARPS = SORT_THREADS / 32;
+    __shared__ int warp_cnt[WARPS][RADIX];
+    __shared__ int running[RADIX];
+    int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    running[threadIdx.x] = hist[threadIdx.x * numTiles + blockIdx.x];
+    int base = blockIdx.x * SORT_TILE;
+    for (int it = 0; it < SORT_ITEMS; it++) {
+#pragma unroll
+        for (int w = 0; w < WARPS; w++) warp_cnt[w][threadIdx.x] = 0;
+        __syncthreads();
+        int i      = base + it * SORT_THREADS + threadIdx.x;
+        bool valid = i < n;
+        unsigned k = valid ? key_in[i] : 0u;
+        int v      = valid ? val_in[i] : 0;
+        unsigned d = valid ? digit_of(k, shift) : RADIX; // invalid lanes get a digit nobody shares
+        unsigned peers = __match_any_sync(0xffffffffu, d);
+        int rank_in_warp = __popc(peers & ((1u << lane) - 1u));
+        if (valid && rank_in_warp == 0) warp_cnt[warp][d] = __popc(peers);
+        __syncthreads();
+        {
+            int dgt = threadIdx.x, acc = running[dgt];
+#pragma unroll
+            for (int w = 0; w < WARPS; w++) {
+                int c = warp_cnt[w][dgt];
+                warp_cnt[w][dgt] = acc;
+                acc += c;
+            }
+            running[dgt] = acc;
+        }
+        __syncthreads();
+        if (valid) {
+            int dst      = warp_cnt[warp][d] + rank_in_warp;
+            key_out[dst] = k;
+            val_out[dst] = v;
+        }
+        __syncthreads();
+    }
+}
+
+// cell_start / cell_end from the sorted keys, and the number of non-ghost particles.
+__global__ void cell_range_kernel(Params P) {
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= P.N) return;
+    unsigned k = P.key[s];
+    if (k == MPSB_GHOST_KEY) return;
+    if (s == 0 || P.key[s - 1] != k) P.cell_start[k] = s;
+    unsigned next = (s == P.N - 1) ? MPSB_GHOST_KEY : P.key[s + 1];
+    if (next != k) P.cell_end[k] = s + 1;
+    if (next == MPSB_GHOST_KEY) *P.n_active = s + 1;
+}
+
+// HOME (id order) -> SORTED (cell order) for every field; also perm and its inverse.
+__global__ void gather_all_kernel(Params P, int from_val) {
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= P.N) return;
+    int id = from_val ? P.val[s] : P.S.id[s];
+    if (from_val) {
+        P.S.id[s]   = id;
+        P.H.inv[id] = s;
+    }
+    const Home& H = P.H;
+    P.S.x[s] = H.pos[3 * id]; P.S.y[s] = H.pos[3 * id + 1]; P.S.z[s] = H.pos[3 * id + 2];
+    P.S.u[s] = H.vel[3 * id]; P.S.v[s] = H.vel[3 * id + 1]; P.S.w[s] = H.vel[3 * id + 2];
+    P.S.ax[s] = H.acc[3 * id]; P.S.ay[s] = H.acc[3 * id + 1]; P.S.az[s] = H.acc[3 * id + 2];
+    P.S.p[s] = H.p[id]; P.S.minp[s] = H.minp[id]; P.S.ratio[s] = H.ratio[id];
+    P.S.type[s] = H.type[id]; P.S.bc[s] = H.bc[id];
+}
+
+// SORTED -> HOME.
+__global__ void scatter_all_kernel(Params P) {
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= P.N) return;
+    int id = P.S.id[s];
+    const Home& H = P.H;
+    H.pos[3 * id] = P.S.x[s]; H.pos[3 * id + 1] = P.S.y[s]; H.pos[3 * id + 2] = P.S.z[s];
+    H.vel[3 * id] = P.S.u[s]; H.vel[3 * id + 1] = P.S.v[s]; H.vel[3 * id + 2] = P.S.w[s];
+    H.acc[3 * id] = P.S.ax[s]; H.acc[3 * id + 1] = P.S.ay[s]; H.acc[3 * id + 2] = P.S.az[s];
+    H.p[id] = P.S.p[s]; H.minp[id] = P.S.minp[s]; H.ratio[id] = P.S.ratio[s];
+    H.type[id] = P.S.type[s]; H.bc[id] = P.S.bc[s];
+}
+
+} // namespace
+
+void mpsb_launch_gather_all(mpsb_handle* h) {
+    Params& P = h->P;
+    MPSB_LAUNCH(h, gather_all_kernel, mpsb_div_up(P.N, 256), 256, 0, P, 0);
+}
+
+void mpsb_launch_scatter_all(mpsb_handle* h) {
+    Params& P = h->P;
+    MPSB_LAUNCH(h, scatter_all_kernel, mpsb_div_up(P.N, 256), 256, 0, P);
+}
+
+// HOME must be current (the caller scatters first when the sorted copy is newer).
+void mpsb_launch_cell_build(mpsb_handle* h) {
+    Params& P   = h->P;
+    int N       = P.N;
+    int grid    = mpsb_div_up(N, 256);
+    int tiles   = mpsb_div_up(N, SORT_TILE);
+    MPSB_LAUNCH(h, key_kernel, grid, 256, 0, P);
+    for (int shift = 0; shift < h->sort_bits; shift += 8) {
+        MPSB_LAUNCH(h, radix_hist_kernel, tiles, SORT_THREADS, 0, P.key, N, shift, tiles, h->block_hist);
+        MPSB_LAUNCH(h, exclusive_scan_kernel, 1, 1024, 0, h->block_hist, RADIX * tiles);
+        MPSB_LAUNCH(h, radix_scatter_kernel, tiles, SORT_THREADS, 0, P.key, P.val, P.key_alt, P.val_alt, N, shift,
+                    tiles, h->block_hist);
+        unsigned* tk = P.key; P.key = P.key_alt; P.key_alt = tk;
+        int* tv = P.val; P.val = P.val_alt; P.val_alt = tv;
+    }
+    cudaMemsetAsync(P.cell_start, 0, sizeof(int) * (size_t) P.numCells, h->stream);
+    cudaMemsetAsync(P.cell_end, 0, sizeof(int) * (size_t) P.numCells, h->stream);
+    cudaMemsetAsync(P.n_active, 0, sizeof(int), h->stream);
+    MPSB_LAUNCH(h, cell_range_kernel, grid, 256, 0, P);
+    MPSB_LAUNCH(h, gather_all_kernel, grid, 256, 0, P, 1);
+}

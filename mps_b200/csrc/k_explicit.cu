@@ -1,0 +1,235 @@
+// k_explicit.cu — explicit half of the step and the final correction:
+//   explicit_kernel   : calcGravity + calcViscosity + moveParticles        (src/mps.cpp:165-215)
+//   collision kernels : collision                                          (src/mps.cpp:217-250)
+//   gradient_kernel   : calcPressureGradient                               (src/mps.cpp:505-533)
+//   move2_kernel      : moveParticlesWithPressureGradient                  (src/mps.cpp:535-545)
+//   courant_kernel    : getCourantNumber                                   (src/mps.cpp:547-571)
+// All sums follow neighbour-list order and every fp64 operation is individually rounded
+// (-fmad=false) so results are bit-identical to the reference.
+#include "mpsb_internal.cuh"
+
+namespace {
+
+// checkBoundaryViolation (src/mps.cpp:643-667): strict '<' on both sides, per axis.
+__device__ __forceinline__ bool out_of_domain(const mpsb_settings& s, double x, double y, double z) {
+    bool in = true;
+    if (x < s.domain_min[0] || s.domain_max[0] < x) in = false;
+    if (y < s.domain_min[1] || s.domain_max[1] < y) in = false;
+    if (z < s.domain_min[2] || s.domain_max[2] < z) in = false;
+    return !in;
+}
+
+__device__ __forceinline__ void ghost_event(const Params& P, int s, double x, double y, double z) {
+    int e = atomicAdd(&P.stats->n_ghosted, 1);
+    if (e < P.ev_cap) {
+        P.ev_ghost_id[e]          = P.S.id[s];
+        P.ev_ghost_xyz[3 * e]     = x;
+        P.ev_ghost_xyz[3 * e + 1] = y;
+        P.ev_ghost_xyz[3 * e + 2] = z;
+    } else {
+        atomicOr(&P.stats->error_flags, 4);
+    }
+}
+
+// Reads neighbours' OLD velocity (u,v,w), writes the new one to (u2,v2,w2); the host swaps.
+__global__ void __launch_bounds__(256) explicit_kernel(Params P) {
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= P.N) return;
+    double u = P.S.u[s], v = P.S.v[s], w = P.S.w[s];
+    if (s < *P.n_active && P.S.type[s] == MPSB_FLUID) {
+        const double re = P.s.re_viscosity;
+        const size_t N  = (size_t) P.N;
+        int cnt = P.nbr_count[s];
+        double tx = 0.0, ty = 0.0, tz = 0.0;
+        for (int k = 0; k < cnt; k++) {
+            double d = P.nbr_dist[k * N + s];
+            if (d < re) {
+                int j      = P.nbr_idx[k * N + s];
+                double wgt = (re / d) - 1.0;
+                tx += (P.S.u[j] - u) * wgt;
+                ty += (P.S.v[j] - v) * wgt;
+                tz += (P.S.w[j] - w) * wgt;
+            }
+        }
+        tx *= P.visc_coef; ty *= P.visc_coef; tz *= P.visc_coef;
+        double ax = P.s.gravity[0] + tx, ay = P.s.gravity[1] + ty, az = P.s.gravity[2] + tz;
+        const double dt = P.s.dt;
+        u += ax * dt; v += ay * dt; w += az * dt;
+        double x = P.S.x[s] + u * dt, y = P.S.y[s] + v * dt, z = P.S.z[s] + w * dt;
+        P.S.x[s] = x; P.S.y[s] = y; P.S.z[s] = z;
+        if (out_of_domain(P.s, x, y, z)) {
+            ghost_event(P, s, x, y, z);
+            P.S.type[s] = MPSB_GHOST;
+        }
+    }
+    P.S.u2[s] = u; P.S.v2[s] = v; P.S.w2[s] = w;
+    P.S.ax[s] = 0.0; P.S.ay[s] = 0.0; P.S.az[s] = 0.0; // acceleration.setZero() for every type (:213)
+}
+
+// ---- collision -----------------------------------------------------------------------------------
+// The reference loop is sequential and in place (Gauss-Seidel): later pairs see earlier updates.
+// Pass 1 (parallel) collects the candidate pairs — list distance < collisionDistance, Fluid i,
+// skipping Fluid j with id >= i — keyed by (id_i, list slot), which is exactly the reference's
+// visiting order. Pass 2 sorts the (few) keys and replays them serially with live positions and
+// velocities. Candidate membership depends only on the stale list distances and on types, neither
+// of which changes during the loop, so the candidate set equals the reference's.
+__global__ void __launch_bounds__(256) collision_candidates_kernel(Params P) {
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= *P.n_active || P.S.type[s] != MPSB_FLUID) return;
+    const size_t N = (size_t) P.N;
+    int cnt = P.nbr_count[s], id = P.S.id[s];
+    for (int k = 0; k < cnt; k++) {
+        double d = P.nbr_dist[k * N + s];
+        if (d < P.s.collision_distance) {
+            int j = P.nbr_idx[k * N + s];
+            if (P.S.type[j] == MPSB_FLUID && P.S.id[j] >= id) continue;
+            int c = atomicAdd(P.cand_count, 1);
+            if (c < P.cand_cap)
+                P.cand[c] = ((unsigned long long) (unsigned) id << 32) | (unsigned) k;
+            else
+                atomicOr(&P.stats->error_flags, 1);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(1024) collision_replay_kernel(Params P) {
+    int M = min(*P.cand_count, P.cand_cap);
+    if (threadIdx.x == 0) P.stats->n_collisions = M;
+    if (M == 0) return;
+    // bitonic sort of the keys in global memory (padded with ~0 to a power of two)
+    int M2 = 1;
+    while (M2 < M) M2 <<= 1;
+    for (int i = M + threadIdx.x; i < M2; i += blockDim.x) P.cand[i] = ~0ull;
+    __syncthreads();
+    for (int size = 2; size <= M2; size <<= 1)
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            for (int t = threadIdx.x; t < (M2 >> 1); t += blockDim.x) {
+                int lo = 2 * t - (t & (stride - 1)), hi = lo + stride;
+                bool up = (lo & size) == 0;
+                unsigned long long a = P.cand[lo], b = P.cand[hi];
+                if ((a > b) == up) {
+                    P.cand[lo] = b;
+                    P.cand[hi] = a;
+                }
+            }
+            __syncthreads();
+        }
+    if (threadIdx.x != 0) return;
+    const size_t N   = (size_t) P.N;
+    const double col = P.s.collision_distance, e = P.s.restitution;
+    for (int c = 0; c < M; c++) {
+        unsigned long long key = P.cand[c];
+        int s = P.H.inv[(int) (key >> 32)], k = (int) (key & 0xffffffffu);
+        int j = P.nbr_idx[k * N + s];
+        double dist = P.nbr_dist[k * N + s];
+        double invMi = P.inv_density;                                       // i is Fluid
+        double invMj = P.S.type[j] == MPSB_FLUID ? P.inv_density : 0.0;    // src/particle.cpp:19-29
+        double reducedMass = 1.0 / (invMi + invMj);
+        double dx = P.S.x[j] - P.S.x[s], dy = P.S.y[j] - P.S.y[s], dz = P.S.z[j] - P.S.z[s];
+        double z2 = (dx * dx + dy * dy) + dz * dz;
+        double nx = dx, ny = dy, nz = dz; // Eigen normalized(): divide by sqrt when > 0
+        if (z2 > 0.0) {
+            double sz = sqrt(z2);
+            nx = dx / sz; ny = dy / sz; nz = dz / sz;
+        }
+        double du = P.S.u[j] - P.S.u[s], dv = P.S.v[j] - P.S.v[s], dw = P.S.w[j] - P.S.w[s];
+        double rel = (du * nx + dv * ny) + dw * nz;
+        if (rel < 0.0) {
+            double impulse = -(1.0 + e) * rel * reducedMass;
+            double ci = impulse * invMi, cj = impulse * invMj;
+            P.S.u[s] -= ci * nx; P.S.v[s] -= ci * ny; P.S.w[s] -= ci * nz;
+            P.S.u[j] += cj * nx; P.S.v[j] += cj * ny; P.S.w[j] += cj * nz;
+            double depth = col - dist;
+            double posImpulse = depth * reducedMass;
+            double pi = posImpulse * invMi, pj = posImpulse * invMj;
+            P.S.x[s] -= pi * nx; P.S.y[s] -= pi * ny; P.S.z[s] -= pi * nz;
+            P.S.x[j] += pj * nx; P.S.y[j] += pj * ny; P.S.z[j] += pj * nz;
+        }
+    }
+}
+
+// ---- pressure gradient and correction ----------------------------------------------------------------
+__global__ void __launch_bounds__(256) gradient_kernel(Params P) {
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= *P.n_active || P.S.type[s] != MPSB_FLUID) return;
+    const double re = P.s.re_pressure;
+    const size_t N  = (size_t) P.N;
+    const double xi = P.S.x[s], yi = P.S.y[s], zi = P.S.z[s], pmin = P.S.minp[s];
+    int cnt = P.nbr_count[s];
+    double gx = 0.0, gy = 0.0, gz = 0.0;
+    for (int k = 0; k < cnt; k++) {
+        double d = P.nbr_dist[k * N + s];
+        if (d < re) {
+            int j = P.nbr_idx[k * N + s];
+            if (P.S.type[j] == MPSB_DUMMY_WALL) continue;
+            double dp = P.S.p[j] - pmin, wgt = (re / d) - 1.0, d2 = d * d;
+            gx += (P.S.x[j] - xi) * dp * wgt / d2;
+            gy += (P.S.y[j] - yi) * dp * wgt / d2;
+            gz += (P.S.z[j] - zi) * dp * wgt / d2;
+        }
+    }
+    gx *= P.grad_coef; gy *= P.grad_coef; gz *= P.grad_coef;
+    P.S.ax[s] = -1.0 * gx / P.s.density;
+    P.S.ay[s] = -1.0 * gy / P.s.density;
+    P.S.az[s] = -1.0 * gz / P.s.density;
+}
+
+__global__ void __launch_bounds__(256) move2_kernel(Params P) {
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= *P.n_active || P.S.type[s] != MPSB_FLUID) return;
+    const double dt = P.s.dt;
+    double ax = P.S.ax[s], ay = P.S.ay[s], az = P.S.az[s];
+    P.S.u[s] += ax * dt; P.S.v[s] += ay * dt; P.S.w[s] += az * dt;
+    double x = P.S.x[s] + ax * dt * dt, y = P.S.y[s] + ay * dt * dt, z = P.S.z[s] + az * dt * dt;
+    P.S.x[s] = x; P.S.y[s] = y; P.S.z[s] = z;
+    if (out_of_domain(P.s, x, y, z)) {
+        ghost_event(P, s, x, y, z);
+        P.S.type[s] = MPSB_GHOST;
+    }
+    // acceleration is deliberately left as is: `pi.acceleration.Zero()` is a no-op (SURVEY B-3)
+}
+
+__global__ void __launch_bounds__(256) courant_kernel(Params P) {
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    double c = 0.0;
+    if (s < *P.n_active && P.S.type[s] == MPSB_FLUID) {
+        double u = P.S.u[s], v = P.S.v[s], w = P.S.w[s];
+        double cc = (sqrt((u * u + v * v) + w * w) * P.s.dt) / P.s.particle_distance;
+        if (cc > c) c = cc; // std::max(max, c): a NaN never replaces the running maximum
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) c = fmax(c, __shfl_xor_sync(0xffffffffu, c, o));
+    // non-negative doubles order like their bit patterns
+    if ((threadIdx.x & 31) == 0 && c > 0.0)
+        atomicMax((unsigned long long*) &P.stats->courant_bits_as_double, (unsigned long long) __double_as_longlong(c));
+}
+
+} // namespace
+
+void mpsb_launch_explicit(mpsb_handle* h) {
+    Params& P = h->P;
+    MPSB_LAUNCH(h, explicit_kernel, mpsb_div_up(P.N, 256), 256, 0, P);
+    double* t;
+    t = P.S.u; P.S.u = P.S.u2; P.S.u2 = t;
+    t = P.S.v; P.S.v = P.S.v2; P.S.v2 = t;
+    t = P.S.w; P.S.w = P.S.w2; P.S.w2 = t;
+}
+
+void mpsb_launch_collision(mpsb_handle* h) {
+    Params& P = h->P;
+    cudaMemsetAsync(P.cand_count, 0, sizeof(int), h->stream);
+    MPSB_LAUNCH(h, collision_candidates_kernel, mpsb_div_up(P.N, 256), 256, 0, P);
+    MPSB_LAUNCH(h, collision_replay_kernel, 1, 1024, 0, P);
+}
+
+void mpsb_launch_gradient_move(mpsb_handle* h) {
+    Params& P = h->P;
+    MPSB_LAUNCH(h, gradient_kernel, mpsb_div_up(P.N, 256), 256, 0, P);
+    MPSB_LAUNCH(h, move2_kernel, mpsb_div_up(P.N, 256), 256, 0, P);
+}
+
+void mpsb_launch_courant(mpsb_handle* h) {
+    Params& P = h->P;
+    cudaMemsetAsync(&P.stats->courant_bits_as_double, 0, sizeof(double), h->stream);
+    MPSB_LAUNCH(h, courant_kernel, mpsb_div_up(P.N, 256), 256, 0, P);
+}

@@ -1,0 +1,92 @@
+// k_neighbors.cu — neighbour-list build and particle number density.
+//
+// Replaces reference MPS::setNeighbors (src/mps.cpp:585-619) and MPS::setNumberDensity /
+// getNumberDensity (:573-583, :627-641). One thread owns one sorted particle and walks the 27
+// cells in the reference's order (jx outer, jy, jz inner; ids ascending inside a cell), so the
+// list ORDER and every distance are bit-identical and all later per-particle sums can follow
+// list order. Lists are slot-major ELL: coalesced stores here and coalesced
+// loads in every consumer.
+#include "mpsb_internal.cuh"
+
+namespace {
+
+__global__ void __launch_bounds__(128) neighbor_kernel(Params P) {
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    int n_active = *P.n_active;
+    if (s >= P.N) return;
+    if (s >= n_active) {
+        P.nbr_count[s] = 0;
+        return;
+    }
+    const double xi = P.S.x[s], yi = P.S.y[s], zi = P.S.z[s];
+    const double re = P.s.re_max;
+    unsigned key = P.key[s];
+    int nxy = P.numX * P.numY;
+    int iz = key / nxy, rem = key - iz * nxy;
+    int iy = rem / P.numX, ix = rem - iy * P.numX;
+    int count = 0;
+    const size_t N = (size_t) P.N;
+    for (int jx = ix - 1; jx <= ix + 1; jx++) {
+        if (jx < 0 || jx >= P.numX) continue;
+        for (int jy = iy - 1; jy <= iy + 1; jy++) {
+            if (jy < 0 || jy >= P.numY) continue;
+            for (int jz = iz - 1; jz <= iz + 1; jz++) {
+                if (jz < 0 || jz >= P.numZ) continue;
+                int c = jx + jy * P.numX + jz * nxy;
+                int b = P.cell_start[c], e = P.cell_end[c];
+                for (int j = b; j < e; j++) {
+                    double dx = P.S.x[j] - xi, dy = P.S.y[j] - yi, dz = P.S.z[j] - zi;
+                    double dist = sqrt((dx * dx + dy * dy) + dz * dz); // Eigen (pj - pi).norm()
+                    if (j != s && dist < re) {
+                        if (count < P.K) {
+                            P.nbr_idx[count * N + s]  = j;
+                            P.nbr_dist[count * N + s] = dist;
+                        }
+                        count++;
+                    }
+                }
+            }
+        }
+    }
+    if (count > P.K) {
+        atomicOr(&P.stats->error_flags, 1);
+        count = P.K;
+    }
+    P.nbr_count[s] = count;
+    // longest list of the step (warp max first to keep atomics rare)
+    int m = count;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0 && m > 0) atomicMax(&P.stats->max_neighbors, m);
+}
+
+// ratio = Surface ? 0 : n(re_p) / n0_p   (src/mps.cpp:630-640); ghosts keep their last value.
+__global__ void number_density_kernel(Params P) {
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= *P.n_active) return;
+    double ratio = 0.0;
+    if (P.S.bc[s] != MPSB_BC_SURFACE) {
+        const double re = P.s.re_pressure;
+        const size_t N  = (size_t) P.N;
+        int cnt = P.nbr_count[s];
+        double n = 0.0;
+        for (int k = 0; k < cnt; k++) {
+            double d = P.nbr_dist[k * N + s];
+            if (d < re) n += mpsb_weight(d, re);
+        }
+        ratio = n / P.s.n0_pressure;
+    }
+    P.S.ratio[s] = ratio;
+}
+
+} // namespace
+
+void mpsb_launch_neighbors(mpsb_handle* h) {
+    Params& P = h->P;
+    MPSB_LAUNCH(h, neighbor_kernel, mpsb_div_up(P.N, 128), 128, 0, P);
+}
+
+void mpsb_launch_number_density(mpsb_handle* h) {
+    Params& P = h->P;
+    MPSB_LAUNCH(h, number_density_kernel, mpsb_div_up(P.N, 256), 256, 0, P);
+}

@@ -1,0 +1,217 @@
+// k_pressure.cu — everything of calcPressure (src/mps.cpp:252-260) except the Krylov solve:
+//   flags_kernel / source_ho_kernel : setBoundaryCondition + setSourceTerm      (:262-320)
+//   matrix_kernel                   : setMatrix, straight from the neighbour lists into ELL (:322-360)
+//   dirichlet_*                     : ensureDirichletBoundaryConnection as connected components (:362-415)
+//   clamp_kernel / min_pressure_kernel : removeNegativePressure + setMinimumPressure (:472-503)
+#include "mpsb_internal.cuh"
+
+namespace {
+
+// Boundary-condition flag for every slot and, for the standard source term, b_i in the same pass
+// over the distances (re_s and re_p sums are kept separate so differing radii stay exact).
+__global__ void __launch_bounds__(256) flags_kernel(Params P) {
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= P.N) return;
+    int bc = MPSB_BC_IGNORED;
+    double b = 0.0;
+    if (s < *P.n_active) {
+        int type = P.S.type[s];
+        if (type != MPSB_GHOST && type != MPSB_DUMMY_WALL) {
+            const double re_s = P.s.re_surface, re_p = P.s.re_pressure;
+            const size_t N = (size_t) P.N;
+            int cnt = P.nbr_count[s];
+            double ns = 0.0, np = 0.0;
+            for (int k = 0; k < cnt; k++) {
+                double d = P.nbr_dist[k * N + s];
+                if (d < re_s) ns += (re_s / d) - 1.0;
+                if (d < re_p) np += (re_p / d) - 1.0;
+            }
+            if (ns < P.beta_n0) {
+                bc = MPSB_BC_SURFACE;
+            } else {
+                bc = MPSB_BC_INNER;
+                // gamma * (1/(dt*dt)) * (n - n0) / n0      (src/mps.cpp:313)
+                b = P.src_std * (np - P.s.n0_pressure) / P.s.n0_pressure;
+            }
+        }
+    }
+    P.S.bc[s] = bc;
+    P.rhs[s]  = b;
+    if (bc == MPSB_BC_INNER) atomicAdd(&P.stats->n_inner, 1);
+    if (bc == MPSB_BC_SURFACE) atomicAdd(&P.stats->n_surface, 1);
+}
+
+// Higher-order source term (src/mps.cpp:288-307); needs the neighbours' flags, hence a second pass.
+__global__ void __launch_bounds__(256) source_ho_kernel(Params P) {
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= *P.n_active || P.S.bc[s] != MPSB_BC_INNER) return;
+    const double re = P.s.re_pressure;
+    const size_t N  = (size_t) P.N;
+    const double xi = P.S.x[s], yi = P.S.y[s], zi = P.S.z[s];
+    const double ui = P.S.u[s], vi = P.S.v[s], wi = P.S.w[s];
+    double b = P.src_ho0 * (P.S.ratio[s] - 1.0);
+    int cnt = P.nbr_count[s];
+    for (int k = 0; k < cnt; k++) {
+        int j = P.nbr_idx[k * N + s];
+        if (P.S.bc[j] == MPSB_BC_IGNORED) continue;
+        double d = P.nbr_dist[k * N + s];
+        if (d < re) {
+            double rx = P.S.x[j] - xi, ry = P.S.y[j] - yi, rz = P.S.z[j] - zi;
+            double ux = P.S.u[j] - ui, uy = P.S.v[j] - vi, uz = P.S.w[j] - wi;
+            double ru = (rx * ux + ry * uy) + rz * uz;
+            b -= P.src_ho1 * ru / (d * d * d);
+        }
+    }
+    P.rhs[s] = b;
+}
+
+// Row s of the PPE: diagonal kept apart, off-diagonals (Inner-Inner only) compacted into ELL slots.
+// a = (2D/(lambda n0)) * w / rho (src/mps.cpp:343); Surface neighbours add to the diagonal only.
+__global__ void __launch_bounds__(256) matrix_kernel(Params P) {
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= P.N) return;
+    int m = 0;
+    double diag = 0.0;
+    if (s < *P.n_active && P.S.bc[s] == MPSB_BC_INNER) {
+        const double re = P.s.re_pressure;
+        const size_t N  = (size_t) P.N;
+        int cnt = P.nbr_count[s];
+        for (int k = 0; k < cnt; k++) {
+            double d = P.nbr_dist[k * N + s];
+            if (d < re) {
+                int j   = P.nbr_idx[k * N + s];
+                int bcj = P.S.bc[j];
+                if (bcj == MPSB_BC_IGNORED) continue;
+                double a = P.mat_coef * ((re / d) - 1.0) / P.s.density;
+                diag += a;
+                if (bcj == MPSB_BC_INNER) {
+                    P.ell_col[m * N + s] = j;
+                    P.ell_val[m * N + s] = -a;
+                    m++;
+                }
+            }
+        }
+        if (P.s.quasi_compressibility_on) diag += P.qc_term;
+        atomicAdd(&P.stats->nnz, m + 1);
+    }
+    P.ell_count[s] = m;
+    P.diag[s]      = diag;
+}
+
+// ---- Dirichlet connectivity ------------------------------------------------------------------------
+// The reference runs a BFS from every Surface particle over the r < re_p graph through ALL
+// non-ghost particles (DummyWall included) and doubles the diagonal of Inner particles it never
+// reaches. The neighbour relation is symmetric, so "reached" == "in a connected component that
+// holds a Surface particle": lock-free union-find (hook larger root under smaller, CAS) + marking.
+__device__ __forceinline__ int uf_find(int* parent, int x) {
+    int p = parent[x];
+    while (p != x) {
+        int gp = parent[p];
+        if (gp != p) parent[x] = gp; // path halving (benign race: only ever points closer to a root)
+        x = p;
+        p = gp;
+    }
+    return x;
+}
+
+__global__ void dirichlet_init_kernel(Params P) {
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= P.N) return;
+    P.parent[s] = s;
+    P.mark[s]   = 0;
+}
+
+__global__ void __launch_bounds__(256) dirichlet_union_kernel(Params P) {
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= *P.n_active) return;
+    const double re = P.s.re_pressure;
+    const size_t N  = (size_t) P.N;
+    int cnt = P.nbr_count[s];
+    for (int k = 0; k < cnt; k++) {
+        int j = P.nbr_idx[k * N + s];
+        if (j > s || !(P.nbr_dist[k * N + s] < re)) continue; // each undirected edge once
+        int a = uf_find(P.parent, s), b = uf_find(P.parent, j);
+        while (a != b) {
+            if (a < b) { int t = a; a = b; b = t; }
+            int old = atomicCAS(&P.parent[a], a, b);
+            if (old == a) break;
+            a = uf_find(P.parent, old);
+            b = uf_find(P.parent, b);
+        }
+    }
+}
+
+__global__ void dirichlet_mark_kernel(Params P) {
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= *P.n_active) return;
+    if (P.S.bc[s] == MPSB_BC_SURFACE) P.mark[uf_find(P.parent, s)] = 1;
+}
+
+__global__ void dirichlet_apply_kernel(Params P) {
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= *P.n_active || P.S.bc[s] != MPSB_BC_INNER) return;
+    if (!P.mark[uf_find(P.parent, s)]) {
+        P.diag[s] *= 2.0; // coefficientMatrix.coeffRef(i, i) *= 2.0 (src/mps.cpp:412)
+        int e = atomicAdd(&P.stats->n_unconnected, 1);
+        if (e < P.ev_cap) P.ev_uncon_id[e] = P.S.id[s];
+    }
+}
+
+// ---- after the solve -----------------------------------------------------------------------------------
+__global__ void clamp_kernel(Params P) {
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= P.N) return;
+    if (P.S.p[s] < 0.0) P.S.p[s] = 0.0; // NaN passes through, like the reference (:475)
+}
+
+__global__ void __launch_bounds__(256) min_pressure_kernel(Params P) {
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= *P.n_active || P.S.bc[s] == MPSB_BC_IGNORED) return;
+    const double re = P.s.re_pressure;
+    const size_t N  = (size_t) P.N;
+    double m = P.S.p[s];
+    int cnt  = P.nbr_count[s];
+    for (int k = 0; k < cnt; k++) {
+        double d = P.nbr_dist[k * N + s];
+        if (d < re) {
+            int j = P.nbr_idx[k * N + s];
+            if (P.S.type[j] == MPSB_DUMMY_WALL) continue;
+            double pj = P.S.p[j];
+            if (m > pj) m = pj;
+        }
+    }
+    P.S.minp[s] = m;
+}
+
+} // namespace
+
+void mpsb_launch_flags_source(mpsb_handle* h) {
+    Params& P = h->P;
+    int grid  = mpsb_div_up(P.N, 256);
+    cudaMemsetAsync(&P.stats->n_inner, 0, 2 * sizeof(int), h->stream); // n_inner, n_surface
+    MPSB_LAUNCH(h, flags_kernel, grid, 256, 0, P);
+    if (P.s.higher_order_source_on) MPSB_LAUNCH(h, source_ho_kernel, grid, 256, 0, P);
+}
+
+void mpsb_launch_matrix(mpsb_handle* h) {
+    Params& P = h->P;
+    cudaMemsetAsync(&P.stats->nnz, 0, sizeof(int), h->stream);
+    MPSB_LAUNCH(h, matrix_kernel, mpsb_div_up(P.N, 256), 256, 0, P);
+}
+
+void mpsb_launch_dirichlet(mpsb_handle* h) {
+    Params& P = h->P;
+    int grid  = mpsb_div_up(P.N, 256);
+    cudaMemsetAsync(&P.stats->n_unconnected, 0, sizeof(int), h->stream);
+    MPSB_LAUNCH(h, dirichlet_init_kernel, grid, 256, 0, P);
+    MPSB_LAUNCH(h, dirichlet_union_kernel, grid, 256, 0, P);
+    MPSB_LAUNCH(h, dirichlet_mark_kernel, grid, 256, 0, P);
+    MPSB_LAUNCH(h, dirichlet_apply_kernel, grid, 256, 0, P);
+}
+
+void mpsb_launch_pressure_post(mpsb_handle* h) {
+    Params& P = h->P;
+    int grid  = mpsb_div_up(P.N, 256);
+    MPSB_LAUNCH(h, clamp_kernel, grid, 256, 0, P);
+    MPSB_LAUNCH(h, min_pressure_kernel, grid, 256, 0, P);
+}

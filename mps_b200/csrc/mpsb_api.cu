@@ -1,0 +1,526 @@
+// mpsb_api.cu — the C ABI of libmps_b200.so (include/mps_b200.h): handle lifetime, state
+// transfer, the step orchestration (reference MPS::stepForward, src/mps.cpp:111-130) and the
+// inspection calls the parity tests use. No CPU fallback anywhere: every compute entry point
+// needs a CUDA device and fails with MPSB_ERR_CUDA otherwise.
+#include "mpsb_internal.cuh"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <utility>
+#include <vector>
+
+namespace {
+
+thread_local char g_create_error[512] = "";
+
+#define CK(h, call)                                                                                   \
+    do {                                                                                              \
+        cudaError_t e_ = (call);                                                                      \
+        if (e_ != cudaSuccess) {                                                                      \
+            snprintf((h)->err, sizeof (h)->err, "%s:%d %s -> %s", __FILE__, __LINE__, #call,          \
+                     cudaGetErrorString(e_));                                                         \
+            (h)->sticky = MPSB_ERR_CUDA;                                                              \
+            return MPSB_ERR_CUDA;                                                                     \
+        }                                                                                             \
+    } while (0)
+
+template <class T>
+cudaError_t dalloc(T** p, size_t count) {
+    cudaError_t e = cudaMalloc((void**) p, sizeof(T) * std::max<size_t>(count, 1));
+    if (e == cudaSuccess) e = cudaMemset(*p, 0, sizeof(T) * std::max<size_t>(count, 1));
+    return e;
+}
+
+void derive(Params& P) {
+    const mpsb_settings& s = P.s;
+    double D  = (double) s.dim;
+    double len = s.re_max;
+    // Bucket::Bucket (src/bucket.cpp:10-22)
+    P.numX = (int) ((s.domain_max[0] - s.domain_min[0]) / len) + 3;
+    P.numY = (int) ((s.domain_max[1] - s.domain_min[1]) / len) + 3;
+    P.numZ = (int) ((s.domain_max[2] - s.domain_min[2]) / len) + 3;
+    P.numCells = P.numX * P.numY * P.numZ;
+    P.visc_coef = (s.kinematic_viscosity) * (2.0 * D) / (s.n0_viscosity * s.lambda_viscosity);
+    P.beta_n0   = s.surface_threshold * s.n0_surface;
+    P.mat_coef  = 2.0 * D / (s.lambda_pressure * s.n0_pressure);
+    P.qc_term   = s.compressibility / (s.dt * s.dt);
+    P.inv_dt2   = 1.0 / (s.dt * s.dt);
+    P.src_std   = s.relaxation_coefficient * (1.0 / (s.dt * s.dt));
+    P.src_ho0   = s.higher_order_gamma * (1.0 / (s.dt * s.dt));
+    P.src_ho1   = (1.0 / (s.n0_pressure * s.dt)) * s.re_pressure;
+    P.grad_coef = D / s.n0_pressure;
+    P.inv_density = 1 / s.density;
+}
+
+int check_flags(mpsb_handle* h) {
+    int f = h->host_stats.error_flags;
+    if (f & 1) {
+        snprintf(h->err, sizeof h->err, "neighbour-list or collision-candidate capacity exceeded (K=%d); "
+                 "set MPSB_MAX_NEIGHBORS", h->P.K);
+        return MPSB_ERR_CAPACITY;
+    }
+    if (f & 2) {
+        snprintf(h->err, sizeof h->err, "a non-ghost particle left the padded cell grid (the reference would "
+                 "index out of bounds here)");
+        return MPSB_ERR_OUT_OF_GRID;
+    }
+    return MPSB_OK;
+}
+
+int fetch_stats(mpsb_handle* h) {
+    CK(h, cudaMemcpyAsync(&h->host_stats, h->P.stats, sizeof(DevStats), cudaMemcpyDeviceToHost, h->stream));
+    CK(h, cudaStreamSynchronize(h->stream));
+    CK(h, cudaGetLastError());
+    return MPSB_OK;
+}
+
+void fill_stats(mpsb_handle* h, mpsb_step_stats* st) {
+    if (!st) return;
+    const DevStats& d = h->host_stats;
+    st->courant         = d.courant_bits_as_double;
+    st->cg_rel_residual = d.cg_rel_residual;
+    st->cg_iterations   = d.cg_iterations;
+    st->n_active        = d.n_active;
+    st->n_inner         = d.n_inner;
+    st->n_surface       = d.n_surface;
+    st->nnz             = d.nnz;
+    st->n_ghosted       = d.n_ghosted;
+    st->n_unconnected   = d.n_unconnected;
+    st->n_collisions    = d.n_collisions;
+    st->max_neighbors   = d.max_neighbors;
+    st->courant_exceeds_cfl = d.courant_bits_as_double > h->P.s.cfl_condition;
+}
+
+void build_lists(mpsb_handle* h) {
+    mpsb_launch_cell_build(h);
+    mpsb_launch_neighbors(h);
+    h->have_lists = true;
+}
+
+} // namespace
+
+extern "C" {
+
+const char* mpsb_version(void) { return "mps_b200 0.1 sm_100a"; }
+
+const char* mpsb_last_error(const mpsb_handle* h) { return h ? h->err : g_create_error; }
+
+int64_t mpsb_num_particles(const mpsb_handle* h) { return h ? h->P.N : 0; }
+int64_t mpsb_launch_count(const mpsb_handle* h) { return h ? h->launches : 0; }
+
+int mpsb_create(const mpsb_settings* settings, int64_t n, const int32_t* type, const double* position,
+                const double* velocity, int device, mpsb_handle** out) {
+    if (!settings || !out || n < 0 || n > 0x7fffffff || (n > 0 && (!type || !position || !velocity))) {
+        snprintf(g_create_error, sizeof g_create_error, "mpsb_create: bad argument");
+        return MPSB_ERR_ARG;
+    }
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0 || device < 0 || device >= ndev) {
+        snprintf(g_create_error, sizeof g_create_error,
+                 "mpsb_create: no usable CUDA device %d (%s); this library has no CPU path", device,
+                 e != cudaSuccess ? cudaGetErrorString(e) : "device count 0 or index out of range");
+        return MPSB_ERR_CUDA;
+    }
+    mpsb_handle* h = new mpsb_handle();
+    memset(h, 0, sizeof *h);
+    h->device = device;
+    h->world  = 1;
+    Params& P = h->P;
+    P.s = *settings;
+    P.N = (int) n;
+    derive(P);
+    const char* envk = getenv("MPSB_MAX_NEIGHBORS");
+    P.K = envk ? atoi(envk) : (settings->dim == 2 ? 64 : 384);
+    if (P.K < 1 || P.numCells <= 0) {
+        snprintf(g_create_error, sizeof g_create_error, "mpsb_create: bad neighbour capacity or cell grid");
+        delete h;
+        return MPSB_ERR_ARG;
+    }
+    h->sort_bits = 8;
+    while (h->sort_bits < 32 && (1ull << h->sort_bits) <= (unsigned long long) P.numCells) h->sort_bits += 8;
+
+#define CKC(call)                                                                                     \
+    do {                                                                                              \
+        cudaError_t e_ = (call);                                                                      \
+        if (e_ != cudaSuccess) {                                                                      \
+            snprintf(g_create_error, sizeof g_create_error, "mpsb_create: %s -> %s", #call,           \
+                     cudaGetErrorString(e_));                                                         \
+            mpsb_destroy(h);                                                                          \
+            return MPSB_ERR_CUDA;                                                                     \
+        }                                                                                             \
+    } while (0)
+
+    CKC(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CKC(cudaGetDeviceProperties(&prop, device));
+    h->num_sms = prop.multiProcessorCount;
+    if (prop.major < 10) {
+        snprintf(g_create_error, sizeof g_create_error, "mpsb_create: device %d is sm_%d%d; this library is built for sm_100a only",
+                 device, prop.major, prop.minor);
+        delete h;
+        return MPSB_ERR_CUDA;
+    }
+    CKC(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
+    h->stream = h->own_stream;
+    for (auto& ev : h->ev) CKC(cudaEventCreate(&ev));
+    size_t N = (size_t) P.N, KN = (size_t) P.K * N;
+    Sorted& S = P.S;
+    double** sd[] = {&S.x, &S.y, &S.z, &S.u, &S.v, &S.w, &S.u2, &S.v2, &S.w2, &S.ax, &S.ay, &S.az, &S.p, &S.minp, &S.ratio};
+    for (double** p : sd) CKC(dalloc(p, N));
+    CKC(dalloc(&S.type, N)); CKC(dalloc(&S.bc, N)); CKC(dalloc(&S.id, N));
+    Home& H = P.H;
+    CKC(dalloc(&H.pos, 3 * N)); CKC(dalloc(&H.vel, 3 * N)); CKC(dalloc(&H.acc, 3 * N));
+    CKC(dalloc(&H.p, N)); CKC(dalloc(&H.minp, N)); CKC(dalloc(&H.ratio, N));
+    CKC(dalloc(&H.type, N)); CKC(dalloc(&H.bc, N)); CKC(dalloc(&H.inv, N));
+    CKC(dalloc(&P.key, N)); CKC(dalloc(&P.key_alt, N)); CKC(dalloc(&P.val, N)); CKC(dalloc(&P.val_alt, N));
+    CKC(dalloc(&P.cell_start, (size_t) P.numCells)); CKC(dalloc(&P.cell_end, (size_t) P.numCells));
+    CKC(dalloc(&P.nbr_count, N)); CKC(dalloc(&P.nbr_idx, KN)); CKC(dalloc(&P.nbr_dist, KN));
+    CKC(dalloc(&P.ell_count, N)); CKC(dalloc(&P.ell_col, KN)); CKC(dalloc(&P.ell_val, KN));
+    CKC(dalloc(&P.diag, N)); CKC(dalloc(&P.rhs, N));
+    CKC(dalloc(&P.cg_r, N)); CKC(dalloc(&P.cg_p, N)); CKC(dalloc(&P.cg_ap, N)); CKC(dalloc(&P.cg_invdiag, N));
+    CKC(dalloc(&P.parent, N)); CKC(dalloc(&P.mark, N));
+    P.cand_cap = 1024;
+    while ((size_t) P.cand_cap < N / 4) P.cand_cap <<= 1;
+    CKC(dalloc(&P.cand, (size_t) P.cand_cap)); CKC(dalloc(&P.cand_count, 1));
+    P.ev_cap = 4096;
+    CKC(dalloc(&P.ev_ghost_id, (size_t) P.ev_cap)); CKC(dalloc(&P.ev_ghost_xyz, 3 * (size_t) P.ev_cap));
+    CKC(dalloc(&P.ev_uncon_id, (size_t) P.ev_cap));
+    CKC(dalloc(&P.stats, 1));
+    P.n_active = &P.stats->n_active;
+    h->block_hist_cap = 256 * (int) ((N + 2047) / 2048 + 1);
+    CKC(dalloc(&h->block_hist, (size_t) h->block_hist_cap));
+    if (mpsb_pcg_configure(h) != 0) {
+        snprintf(g_create_error, sizeof g_create_error, "mpsb_create: PCG kernel cannot be made resident");
+        mpsb_destroy(h);
+        return MPSB_ERR_CUDA;
+    }
+    CKC(dalloc(&P.cg_partials, 3 * (size_t) h->cg_max_blocks));
+    // initial state: type/position/velocity from the caller, everything else 0 / Ignored (SURVEY B-1)
+    CKC(cudaMemcpy(H.type, type, sizeof(int) * N, cudaMemcpyHostToDevice));
+    CKC(cudaMemcpy(H.pos, position, sizeof(double) * 3 * N, cudaMemcpyHostToDevice));
+    CKC(cudaMemcpy(H.vel, velocity, sizeof(double) * 3 * N, cudaMemcpyHostToDevice));
+    if (N > 0) build_lists(h);
+    CKC(cudaStreamSynchronize(h->stream));
+    CKC(cudaGetLastError());
+#undef CKC
+    *out = h;
+    return MPSB_OK;
+}
+
+int mpsb_destroy(mpsb_handle* h) {
+    if (!h) return MPSB_OK;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    Params& P = h->P;
+    Sorted& S = P.S;
+    Home& H   = P.H;
+    void* ptrs[] = {S.x, S.y, S.z, S.u, S.v, S.w, S.u2, S.v2, S.w2, S.ax, S.ay, S.az, S.p, S.minp, S.ratio, S.type,
+                    S.bc, S.id, H.pos, H.vel, H.acc, H.p, H.minp, H.ratio, H.type, H.bc, H.inv, P.key, P.key_alt,
+                    P.val, P.val_alt, P.cell_start, P.cell_end, P.nbr_count, P.nbr_idx, P.nbr_dist, P.ell_count,
+                    P.ell_col, P.ell_val, P.diag, P.rhs, P.cg_r, P.cg_p, P.cg_ap, P.cg_invdiag, P.cg_partials,
+                    P.parent, P.mark, P.cand, P.cand_count, P.ev_ghost_id, P.ev_ghost_xyz, P.ev_uncon_id, P.stats,
+                    h->block_hist};
+    for (void* p : ptrs)
+        if (p) cudaFree(p);
+    for (auto& ev : h->ev)
+        if (ev) cudaEventDestroy(ev);
+    if (h->own_stream) cudaStreamDestroy(h->own_stream);
+    delete h;
+    return MPSB_OK;
+}
+
+int mpsb_upload(mpsb_handle* h, uint32_t mask, const mpsb_fields* f) {
+    if (!h || !f) return MPSB_ERR_ARG;
+    if (h->sticky) return h->sticky;
+    CK(h, cudaSetDevice(h->device));
+    size_t N = (size_t) h->P.N;
+    Home& H  = h->P.H;
+    cudaStream_t st = h->stream;
+#define UP(bit, dst, src, bytes)                                                                  \
+    if ((mask & (bit)) && (src)) CK(h, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, st))
+    UP(MPSB_F_TYPE, H.type, f->type, sizeof(int) * N);
+    UP(MPSB_F_POSITION, H.pos, f->position, sizeof(double) * 3 * N);
+    UP(MPSB_F_VELOCITY, H.vel, f->velocity, sizeof(double) * 3 * N);
+    UP(MPSB_F_ACCEL, H.acc, f->acceleration, sizeof(double) * 3 * N);
+    UP(MPSB_F_PRESSURE, H.p, f->pressure, sizeof(double) * N);
+    UP(MPSB_F_MIN_PRESSURE, H.minp, f->minimum_pressure, sizeof(double) * N);
+    UP(MPSB_F_NUMBER_DENSITY_RATIO, H.ratio, f->number_density_ratio, sizeof(double) * N);
+    UP(MPSB_F_BOUNDARY_CONDITION, H.bc, f->boundary_condition, sizeof(int) * N);
+#undef UP
+    if (h->have_lists && N > 0) mpsb_launch_gather_all(h); // keep the sorted working set in step
+    CK(h, cudaStreamSynchronize(st));
+    return MPSB_OK;
+}
+
+int mpsb_upload_device(mpsb_handle* h, const int32_t* d_type, const double* d_position, const double* d_velocity) {
+    if (!h) return MPSB_ERR_ARG;
+    if (h->sticky) return h->sticky;
+    CK(h, cudaSetDevice(h->device));
+    size_t N = (size_t) h->P.N;
+    Home& H  = h->P.H;
+    if (d_type) CK(h, cudaMemcpyAsync(H.type, d_type, sizeof(int) * N, cudaMemcpyDeviceToDevice, h->stream));
+    if (d_position) CK(h, cudaMemcpyAsync(H.pos, d_position, sizeof(double) * 3 * N, cudaMemcpyDeviceToDevice, h->stream));
+    if (d_velocity) CK(h, cudaMemcpyAsync(H.vel, d_velocity, sizeof(double) * 3 * N, cudaMemcpyDeviceToDevice, h->stream));
+    if (h->have_lists && N > 0) mpsb_launch_gather_all(h);
+    CK(h, cudaStreamSynchronize(h->stream));
+    return MPSB_OK;
+}
+
+int mpsb_download(mpsb_handle* h, uint32_t mask, const mpsb_fields* f) {
+    if (!h || !f) return MPSB_ERR_ARG;
+    if (h->sticky) return h->sticky;
+    CK(h, cudaSetDevice(h->device));
+    size_t N = (size_t) h->P.N;
+    Home& H  = h->P.H;
+    cudaStream_t st = h->stream;
+#define DN(bit, dst, src, bytes)                                                                  \
+    if ((mask & (bit)) && (dst)) CK(h, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, st))
+    DN(MPSB_F_TYPE, f->type, H.type, sizeof(int) * N);
+    DN(MPSB_F_POSITION, f->position, H.pos, sizeof(double) * 3 * N);
+    DN(MPSB_F_VELOCITY, f->velocity, H.vel, sizeof(double) * 3 * N);
+    DN(MPSB_F_ACCEL, f->acceleration, H.acc, sizeof(double) * 3 * N);
+    DN(MPSB_F_PRESSURE, f->pressure, H.p, sizeof(double) * N);
+    DN(MPSB_F_MIN_PRESSURE, f->minimum_pressure, H.minp, sizeof(double) * N);
+    DN(MPSB_F_NUMBER_DENSITY_RATIO, f->number_density_ratio, H.ratio, sizeof(double) * N);
+    DN(MPSB_F_BOUNDARY_CONDITION, f->boundary_condition, H.bc, sizeof(int) * N);
+#undef DN
+    CK(h, cudaStreamSynchronize(st));
+    return MPSB_OK;
+}
+
+// MPS::stepForward (src/mps.cpp:111-130). HOME is current on entry and on exit.
+int mpsb_step(mpsb_handle* h, int want_number_density, mpsb_step_stats* stats) {
+    if (!h) return MPSB_ERR_ARG;
+    if (h->sticky) return h->sticky;
+    if (stats) memset(stats, 0, sizeof *stats);
+    if (h->P.N == 0) return MPSB_OK;
+    CK(h, cudaSetDevice(h->device));
+    cudaStream_t st = h->stream;
+    cudaEvent_t* E  = h->ev;
+    CK(h, cudaMemsetAsync(h->P.stats, 0, sizeof(DevStats), st));
+    CK(h, cudaEventRecord(E[0], st));
+    build_lists(h);                                  // setNeighbors
+    CK(h, cudaEventRecord(E[1], st));
+    mpsb_launch_explicit(h);                         // calcGravity, calcViscosity, moveParticles
+    CK(h, cudaEventRecord(E[2], st));
+    mpsb_launch_scatter_all(h);
+    build_lists(h);                                  // setNeighbors
+    CK(h, cudaEventRecord(E[3], st));
+    mpsb_launch_collision(h);                        // collision
+    CK(h, cudaEventRecord(E[4], st));
+    mpsb_launch_scatter_all(h);
+    build_lists(h);                                  // setNeighbors
+    CK(h, cudaEventRecord(E[5], st));
+    mpsb_launch_flags_source(h);                     // calcPressure ...
+    mpsb_launch_matrix(h);
+    mpsb_launch_dirichlet(h);
+    CK(h, cudaEventRecord(E[6], st));
+    mpsb_launch_pcg(h);
+    CK(h, cudaEventRecord(E[7], st));
+    mpsb_launch_pressure_post(h);
+    mpsb_launch_gradient_move(h);                    // calcPressureGradient, moveParticlesWithPressureGradient
+    CK(h, cudaEventRecord(E[8], st));
+    if (want_number_density) {                       // setNumberDensity (:125-127)
+        mpsb_launch_scatter_all(h);
+        build_lists(h);
+        mpsb_launch_number_density(h);
+    }
+    CK(h, cudaEventRecord(E[9], st));
+    mpsb_launch_courant(h);                          // getCourantNumber
+    mpsb_launch_scatter_all(h);
+    CK(h, cudaEventRecord(E[10], st));
+    int rc = fetch_stats(h);
+    if (rc) return rc;
+    fill_stats(h, stats);
+    if (stats) {
+        auto ms = [&](int a, int b) {
+            float t = 0.f;
+            cudaEventElapsedTime(&t, E[a], E[b]);
+            return (double) t;
+        };
+        stats->ms_neighbors = ms(0, 1) + ms(2, 3) + ms(4, 5) + ms(8, 9);
+        stats->ms_explicit  = ms(1, 2);
+        stats->ms_collision = ms(3, 4);
+        stats->ms_assemble  = ms(5, 6);
+        stats->ms_solve     = ms(6, 7);
+        stats->ms_correct   = ms(7, 8) + ms(9, 10);
+        stats->ms_total     = ms(0, 10);
+    }
+    return check_flags(h);
+}
+
+int mpsb_run_phase(mpsb_handle* h, int phase, mpsb_step_stats* stats) {
+    if (!h) return MPSB_ERR_ARG;
+    if (h->sticky) return h->sticky;
+    if (stats) memset(stats, 0, sizeof *stats);
+    if (h->P.N == 0) return MPSB_OK;
+    CK(h, cudaSetDevice(h->device));
+    CK(h, cudaMemsetAsync(&h->P.stats->error_flags, 0, sizeof(int), h->stream));
+    switch (phase) {
+    case MPSB_PH_NEIGHBORS:
+        CK(h, cudaMemsetAsync(&h->P.stats->max_neighbors, 0, sizeof(int), h->stream));
+        build_lists(h);
+        break;
+    case MPSB_PH_EXPLICIT:
+        CK(h, cudaMemsetAsync(&h->P.stats->n_ghosted, 0, sizeof(int), h->stream));
+        mpsb_launch_explicit(h);
+        break;
+    case MPSB_PH_COLLISION: mpsb_launch_collision(h); break;
+    case MPSB_PH_FLAGS_SOURCE: mpsb_launch_flags_source(h); break;
+    case MPSB_PH_MATRIX: mpsb_launch_matrix(h); break;
+    case MPSB_PH_DIRICHLET: mpsb_launch_dirichlet(h); break;
+    case MPSB_PH_SOLVE: mpsb_launch_pcg(h); break;
+    case MPSB_PH_PRESSURE_POST: mpsb_launch_pressure_post(h); break;
+    case MPSB_PH_GRADIENT_MOVE:
+        CK(h, cudaMemsetAsync(&h->P.stats->n_ghosted, 0, sizeof(int), h->stream));
+        mpsb_launch_gradient_move(h);
+        break;
+    case MPSB_PH_NUMBER_DENSITY:
+        build_lists(h);
+        mpsb_launch_number_density(h);
+        break;
+    case MPSB_PH_COURANT: mpsb_launch_courant(h); break;
+    default: snprintf(h->err, sizeof h->err, "unknown phase %d", phase); return MPSB_ERR_ARG;
+    }
+    mpsb_launch_scatter_all(h);
+    int rc = fetch_stats(h);
+    if (rc) return rc;
+    fill_stats(h, stats);
+    return check_flags(h);
+}
+
+int mpsb_get_neighbors(mpsb_handle* h, int64_t* row_start, int32_t* ids, double* dist, int64_t capacity,
+                       int64_t* total) {
+    if (!h || !row_start || !total) return MPSB_ERR_ARG;
+    if (h->sticky) return h->sticky;
+    CK(h, cudaSetDevice(h->device));
+    CK(h, cudaStreamSynchronize(h->stream));
+    const Params& P = h->P;
+    size_t N = (size_t) P.N;
+    std::vector<int> cnt(N), inv(N), sid(N), type(N);
+    CK(h, cudaMemcpy(cnt.data(), P.nbr_count, sizeof(int) * N, cudaMemcpyDeviceToHost));
+    CK(h, cudaMemcpy(inv.data(), P.H.inv, sizeof(int) * N, cudaMemcpyDeviceToHost));
+    CK(h, cudaMemcpy(sid.data(), P.S.id, sizeof(int) * N, cudaMemcpyDeviceToHost));
+    CK(h, cudaMemcpy(type.data(), P.H.type, sizeof(int) * N, cudaMemcpyDeviceToHost));
+    int kmax = 0;
+    for (size_t s = 0; s < N; s++) kmax = std::max(kmax, cnt[s]);
+    int64_t k = 0;
+    for (size_t i = 0; i < N; i++) {
+        row_start[i] = k;
+        if (type[i] != MPSB_GHOST) k += cnt[inv[i]];
+    }
+    row_start[N] = k;
+    *total       = k;
+    if (!ids || !dist) return MPSB_OK;
+    if (capacity < k) return MPSB_ERR_CAPACITY;
+    std::vector<int> idx((size_t) kmax * N);
+    std::vector<double> dd((size_t) kmax * N);
+    if (kmax > 0) {
+        CK(h, cudaMemcpy(idx.data(), P.nbr_idx, sizeof(int) * idx.size(), cudaMemcpyDeviceToHost));
+        CK(h, cudaMemcpy(dd.data(), P.nbr_dist, sizeof(double) * dd.size(), cudaMemcpyDeviceToHost));
+    }
+    for (size_t i = 0; i < N; i++) {
+        if (type[i] == MPSB_GHOST) continue;
+        size_t s = (size_t) inv[i];
+        for (int m = 0; m < cnt[s]; m++) {
+            ids[row_start[i] + m]  = sid[idx[(size_t) m * N + s]];
+            dist[row_start[i] + m] = dd[(size_t) m * N + s];
+        }
+    }
+    return MPSB_OK;
+}
+
+int mpsb_get_ppe(mpsb_handle* h, int64_t* row_start, int32_t* col, double* val, double* rhs, int64_t capacity,
+                 int64_t* nnz) {
+    if (!h || !row_start || !nnz) return MPSB_ERR_ARG;
+    if (h->sticky) return h->sticky;
+    CK(h, cudaSetDevice(h->device));
+    CK(h, cudaStreamSynchronize(h->stream));
+    const Params& P = h->P;
+    size_t N = (size_t) P.N;
+    std::vector<int> cnt(N), inv(N), sid(N), bc(N);
+    std::vector<double> diag(N), b(N);
+    CK(h, cudaMemcpy(cnt.data(), P.ell_count, sizeof(int) * N, cudaMemcpyDeviceToHost));
+    CK(h, cudaMemcpy(inv.data(), P.H.inv, sizeof(int) * N, cudaMemcpyDeviceToHost));
+    CK(h, cudaMemcpy(sid.data(), P.S.id, sizeof(int) * N, cudaMemcpyDeviceToHost));
+    CK(h, cudaMemcpy(bc.data(), P.S.bc, sizeof(int) * N, cudaMemcpyDeviceToHost));
+    CK(h, cudaMemcpy(diag.data(), P.diag, sizeof(double) * N, cudaMemcpyDeviceToHost));
+    CK(h, cudaMemcpy(b.data(), P.rhs, sizeof(double) * N, cudaMemcpyDeviceToHost));
+    int kmax = 0;
+    for (size_t s = 0; s < N; s++) kmax = std::max(kmax, cnt[s]);
+    int64_t k = 0;
+    for (size_t i = 0; i < N; i++) {
+        row_start[i] = k;
+        size_t s = (size_t) inv[i];
+        if (bc[s] == MPSB_BC_INNER) k += cnt[s] + 1;
+        if (rhs) rhs[i] = b[s];
+    }
+    row_start[N] = k;
+    *nnz         = k;
+    if (!col || !val) return MPSB_OK;
+    if (capacity < k) return MPSB_ERR_CAPACITY;
+    std::vector<int> ec((size_t) kmax * N);
+    std::vector<double> ev((size_t) kmax * N);
+    if (kmax > 0) {
+        CK(h, cudaMemcpy(ec.data(), P.ell_col, sizeof(int) * ec.size(), cudaMemcpyDeviceToHost));
+        CK(h, cudaMemcpy(ev.data(), P.ell_val, sizeof(double) * ev.size(), cudaMemcpyDeviceToHost));
+    }
+    std::vector<std::pair<int, double>> row;
+    for (size_t i = 0; i < N; i++) {
+        size_t s = (size_t) inv[i];
+        if (bc[s] != MPSB_BC_INNER) continue;
+        row.clear();
+        for (int m = 0; m < cnt[s]; m++) row.push_back({sid[ec[(size_t) m * N + s]], ev[(size_t) m * N + s]});
+        row.push_back({(int) i, diag[s]});
+        std::sort(row.begin(), row.end(), [](const auto& a, const auto& c) { return a.first < c.first; });
+        for (size_t m = 0; m < row.size(); m++) {
+            col[row_start[i] + (int64_t) m] = row[m].first;
+            val[row_start[i] + (int64_t) m] = row[m].second;
+        }
+    }
+    return MPSB_OK;
+}
+
+int mpsb_set_stream(mpsb_handle* h, void* cuda_stream) {
+    if (!h) return MPSB_ERR_ARG;
+    if (h->sticky) return h->sticky;
+    CK(h, cudaSetDevice(h->device));
+    CK(h, cudaStreamSynchronize(h->stream));
+    h->stream = cuda_stream ? (cudaStream_t) cuda_stream : h->own_stream;
+    return MPSB_OK;
+}
+
+int mpsb_events(mpsb_handle* h, int kind, int32_t* ids, double* xyz, int capacity, int* count) {
+    if (!h || !count) return MPSB_ERR_ARG;
+    if (h->sticky) return h->sticky;
+    CK(h, cudaSetDevice(h->device));
+    int n = kind == 0 ? h->host_stats.n_ghosted : h->host_stats.n_unconnected;
+    n     = std::min(n, h->P.ev_cap);
+    *count = n;
+    int m = std::min(n, capacity);
+    if (m > 0 && ids)
+        CK(h, cudaMemcpy(ids, kind == 0 ? h->P.ev_ghost_id : h->P.ev_uncon_id, sizeof(int) * m, cudaMemcpyDeviceToHost));
+    if (m > 0 && xyz && kind == 0)
+        CK(h, cudaMemcpy(xyz, h->P.ev_ghost_xyz, sizeof(double) * 3 * m, cudaMemcpyDeviceToHost));
+    return MPSB_OK;
+}
+
+} // extern "C"
+
+// ---- multi-GPU attachment: implemented in mpsb_comm.cu when built with NCCL ------------------------
+#ifndef MPSB_WITH_NCCL
+extern "C" int mpsb_comm_unique_id(void* out128) {
+    (void) out128;
+    return MPSB_ERR_COMM;
+}
+extern "C" int mpsb_attach_comm(mpsb_handle* h, int rank, int world_size, const void* id) {
+    (void) rank; (void) world_size; (void) id;
+    if (h) snprintf(h->err, sizeof h->err, "library built without NCCL");
+    return MPSB_ERR_COMM;
+}
+#endif

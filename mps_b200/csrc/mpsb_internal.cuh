@@ -1,0 +1,154 @@
+// mpsb_internal.cuh — device-state layout and kernel entry points shared by the .cu files of
+// libmps_b200.so (sm_100a only). See DESIGN.md §3 for the layout rationale.
+//
+// Two views of the particle state live in HBM:
+//   * HOME  (id order, packed xyz)  — what upload/download move; authoritative between API calls.
+//   * SORTED (cell-major, then id; SoA) — the working set of every kernel of the step. Built by
+//     the cell-list build (key -> radix sort -> gather); all neighbour indices are SORTED indices.
+// Neighbour lists and the PPE matrix are slot-major ELL: entry k of row s lives at [k * N + s],
+// so a warp that owns 32 consecutive rows reads 32 consecutive values per slot (coalesced).
+#pragma once
+#include "../../include/mps_b200.h"
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define MPSB_GHOST_KEY 0xFFFFFFFFu
+
+// Device-side per-step counters, copied to the host once per step.
+struct DevStats {
+    double courant_bits_as_double; // written through atomicMax on the bit pattern
+    double cg_rel_residual;
+    double rhs_norm2;
+    int cg_iterations;
+    int n_active;
+    int n_inner;
+    int n_surface;
+    int nnz;
+    int n_ghosted;
+    int n_unconnected;
+    int n_collisions;
+    int max_neighbors;
+    int error_flags; // bit0 capacity, bit1 out-of-grid, bit2 event overflow
+    int pad[2];
+};
+
+// Sorted-order SoA working set (all arrays have N entries).
+struct Sorted {
+    double *x, *y, *z;       // position
+    double *u, *v, *w;       // velocity
+    double *u2, *v2, *w2;    // velocity double buffer (explicit step reads neighbours' old velocity)
+    double *ax, *ay, *az;    // acceleration
+    double *p, *minp, *ratio;
+    int *type;               // ParticleType values
+    int *bc;                 // BoundaryCondition values
+    int *id;                 // perm: sorted index -> particle id
+};
+
+struct Home {
+    double *pos, *vel, *acc; // packed xyz, 3N
+    double *p, *minp, *ratio;
+    int *type, *bc;
+    int *inv;                // particle id -> sorted index (valid after a build)
+};
+
+// Everything a kernel needs, passed by value.
+struct Params {
+    mpsb_settings s;
+    int N;        // particle slots (ghosts included)
+    int K;        // neighbour-list capacity per particle
+    int numX, numY, numZ, numCells;
+    // derived coefficients, computed on the host with the reference's operation order
+    double visc_coef;    // nu * (2*dim) / (n0_v * lambda_v)          src/mps.cpp:182
+    double beta_n0;      // beta * n0_s                               src/mps.cpp:271
+    double mat_coef;     // 2*dim / (lambda_p * n0_p)                 src/mps.cpp:343
+    double qc_term;      // alpha / (dt*dt)                           src/mps.cpp:354
+    double inv_dt2;      // 1 / (dt*dt)
+    double src_std;      // gamma_relax * (1/(dt*dt))                 src/mps.cpp:313
+    double src_ho0;      // gamma_ho * (1/(dt*dt))                    src/mps.cpp:290
+    double src_ho1;      // (1/(n0_p*dt)) * re_p                      src/mps.cpp:304
+    double grad_coef;    // dim / n0_p                                src/mps.cpp:530
+    double inv_density;  // 1 / density                               src/particle.cpp:22
+    Sorted S;
+    Home H;
+    // cell list
+    unsigned *key, *key_alt;   // N each (sorted keys end up in `key`)
+    int *val, *val_alt;        // N each (ids)
+    int *cell_start, *cell_end; // numCells each
+    // neighbour ELL
+    int *nbr_count;            // N
+    int *nbr_idx;              // K*N
+    double *nbr_dist;          // K*N
+    // PPE: ELL off-diagonals + diagonal + rhs; CG vectors
+    int *ell_count;            // N
+    int *ell_col;              // K*N
+    double *ell_val;           // K*N
+    double *diag, *rhs;        // N
+    double *cg_r, *cg_p, *cg_ap, *cg_invdiag; // N
+    double *cg_partials;       // 3 * max_blocks
+    // Dirichlet connectivity
+    int *parent;               // N
+    int *mark;                 // N
+    // collision candidates
+    unsigned long long *cand;  // cand_cap
+    int cand_cap;
+    int *cand_count;
+    // events
+    int *ev_ghost_id; double *ev_ghost_xyz; int *ev_uncon_id; int ev_cap;
+    DevStats* stats;
+    int* n_active; // == &stats->n_active
+};
+
+struct mpsb_handle {
+    Params P;
+    int device;
+    cudaStream_t stream;
+    cudaStream_t own_stream;
+    cudaEvent_t ev[16];
+    int sort_bits;
+    int cg_max_blocks;      // cooperative grid limit for the PCG kernel
+    int cg_threads;
+    int num_sms;
+    int64_t launches;
+    bool have_lists;        // a neighbour build has happened since the last position upload
+    DevStats host_stats;
+    char err[512];
+    int sticky;
+    // scratch for the radix sort
+    int* block_hist; int block_hist_cap;
+    void* comm; int rank, world; // multi-GPU (mpsb_comm.cu)
+    // host staging for inspection calls
+};
+
+// ---- launchers (each file owns its kernels) ----------------------------------------------------
+void mpsb_launch_cell_build(mpsb_handle* h);            // k_cells.cu: scatter->key->sort->ranges->gather
+void mpsb_launch_gather_all(mpsb_handle* h);            // HOME -> SORTED with the current perm
+void mpsb_launch_scatter_all(mpsb_handle* h);           // SORTED -> HOME
+void mpsb_launch_neighbors(mpsb_handle* h);             // k_neighbors.cu
+void mpsb_launch_number_density(mpsb_handle* h);
+void mpsb_launch_explicit(mpsb_handle* h);              // k_explicit.cu
+void mpsb_launch_collision(mpsb_handle* h);
+void mpsb_launch_gradient_move(mpsb_handle* h);
+void mpsb_launch_courant(mpsb_handle* h);
+void mpsb_launch_flags_source(mpsb_handle* h);          // k_pressure.cu
+void mpsb_launch_matrix(mpsb_handle* h);
+void mpsb_launch_dirichlet(mpsb_handle* h);
+void mpsb_launch_pressure_post(mpsb_handle* h);
+void mpsb_launch_pcg(mpsb_handle* h);                   // k_pcg.cu
+int mpsb_pcg_configure(mpsb_handle* h);
+
+#define MPSB_LAUNCH(h, kernel, grid, block, smem, ...)                                   \
+    do {                                                                                 \
+        kernel<<<(grid), (block), (smem), (h)->stream>>>(__VA_ARGS__);                   \
+        (h)->launches++;                                                                 \
+    } while (0)
+
+static inline int mpsb_div_up(int a, int b) { return (a + b - 1) / b; }
+
+#ifdef __CUDACC__
+// weight (reference src/mps.cpp:9-16); every operation individually rounded (no FMA: the
+// library is compiled with -fmad=false)
+__device__ __forceinline__ double mpsb_weight(double dist, double re) {
+    return dist < re ? (re / dist) - 1.0 : 0.0;
+}
+#endif
