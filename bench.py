@@ -1,0 +1,333 @@
+#!/usr/bin/env python
+"""bench.py — the MPS time step (reference MPS::stepForward, src/mps.cpp:111-130) on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--nx NX]
+
+Workload (BASELINE.json configs[3], the configuration the metric "particle-steps/sec and PPE solve
+ms/step at 1/2/4/8 B200; % of HBM roofline" is quoted on): the synthetic scaled dam break —
+dambreak_fine geometry and settings, l0 = 0.4/NX, dt/l0 kept — NX = 2832 -> 4 042 868 particles
+(4 010 112 fluid), generated in memory. A "step" is one MPS::stepForward of the running simulation.
+
+One JSON line on stdout (rank 0). `value` = non-ghost particles x steps / device time with the state
+resident in HBM; `e2e` = the same through the host-buffer C ABI (upload from pinned host memory, step,
+download) every step; `roofline` describes the dominant kernel (the persistent PCG solve);
+`cpu_baseline` times the compiled reference (oracle/_ref) on this box's host cores on a bounded sample.
+
+--impl reference: the reference's own CPU implementation (oracle/_ref/libmps_ref.so, the unmodified
+sources compiled by oracle/Makefile; the oracle port if that file is absent), same metric and unit.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "particle_steps_per_sec"
+UNIT = "particle-steps/s"
+DEFAULT_NX = 2832
+CPU_SAMPLE_NX = 400  # 84 518 particles: ~10 s per reference step on one Xeon core
+
+
+def workload_config(nx, n_particles, parallelism):
+    return {
+        "workload": f"synthetic scaled dam break (BASELINE configs[3]): dambreak_fine geometry/settings, "
+                    f"l0=0.4/{nx}, dt/l0=0.125 s/m",
+        "nx_fluid": nx,
+        "particles": int(n_particles),
+        "parallelism": parallelism,
+        "l2_policy": "working set (neighbour lists + PPE, >4 GB at nx=2832) exceeds the 126 MB L2; no flush needed",
+    }
+
+
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200", "-i",
+                 str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, smmax, power, reasons = [], None, [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                smmax = float(f[2])
+                power.append(float(f[3]))
+            except ValueError:
+                continue
+            for name, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": smmax,
+                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------------
+def cpu_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def make_cpu_mps(nx):
+    """The reference CPU implementation of the path on the scaled dam break: (object, kind, n_active)."""
+    import numpy as np
+
+    from mps_b200 import cases as C
+    from oracle import refbind as R
+
+    S, t, p, v = C.scaled_dambreak(nx)
+    if R.have_ref():
+        d = tempfile.mkdtemp(prefix="mpsb_bench_")
+        yml = C.write_settings_yaml(S, os.path.join(d, "settings.yml"))
+        return R.RefMPS(yml, arrays=(t, p, v)), "reference", int(np.count_nonzero(t != C.GHOST))
+    if not R.have_oracle():
+        subprocess.run(["make", "-C", os.path.join(ROOT, "oracle"), "oracle"], check=True, capture_output=True)
+    return R.OracleMPS(S.to_c(), t, p, v), "port", int(np.count_nonzero(t != C.GHOST))
+
+
+def time_cpu_steps(nx, steps, warmup, budget_s=None):
+    mps, kind, n_active = make_cpu_mps(nx)
+    for _ in range(warmup):
+        mps.step(False)
+    times = []
+    t_begin = time.perf_counter()
+    for k in range(steps):
+        t0 = time.perf_counter()
+        mps.step(False)
+        times.append(time.perf_counter() - t0)
+        if budget_s is not None and time.perf_counter() - t_begin > budget_s:
+            break
+    mps.close()
+    return kind, n_active, times
+
+
+def cpu_sample_text(nx, n, kind, nsteps):
+    what = ("the unmodified reference (oracle/_ref/libmps_ref.so; it solves the PPE twice per step, "
+            "src/mps.cpp:457,460)" if kind == "reference" else "the oracle port (oracle/mps_oracle.cpp)")
+    return (f"{nsteps} step(s) of {what} on the same generator at nx_fluid={nx} ({n} particles); CG iterations "
+            f"grow ~1/l0, so the full-size CPU figure is lower still (see extrapolated_full_size)")
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    nx_cpu = args.cpu_nx
+    # keep the whole run within a few minutes: cost/step ~ 11 s * (nx/400)^3 on one core
+    total = max(1, args.steps + args.warmup)
+    while nx_cpu > 80 and 11.0 * (nx_cpu / 400.0) ** 3 * total > 240.0:
+        nx_cpu -= 40
+    kind, n, times = time_cpu_steps(nx_cpu, args.steps, args.warmup)
+    from mps_b200 import cases as C
+
+    n_full = len(C.scaled_dambreak(args.nx)[1])
+    sec = sum(times)
+    value = n * len(times) / sec
+    out = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": len(times), "warmup": args.warmup, "ms_per_step": 1e3 * sec / len(times), "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args.nx, n_full, "cpu"),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cpu_threads(), "kind": kind,
+                         "sample": cpu_sample_text(nx_cpu, n, kind, len(times)),
+                         "extrapolated_full_size": value * (nx_cpu / args.nx)},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(out), flush=True)
+    return 0
+
+
+# ------------------------------------------------------------------------------------------------
+def run_gpu_arm(args):
+    import numpy as np
+    import torch
+
+    from mps_b200 import capi, cases as C
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the MPS step has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    S, t, p, v = C.scaled_dambreak(args.nx)
+    n_active0 = int(np.count_nonzero(t != C.GHOST))
+    dev = capi.DeviceMPS(S, t, p, v, device=local)
+    if world > 1:
+        dev.attach_comm_torch(rank, world)
+    stream = torch.cuda.current_stream()
+    dev.set_stream(stream.cuda_stream)
+    dev.load_initial_state()
+
+    def barrier():
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        dev.step_forward(False)
+    sampler = ClockSampler(local)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    launches0 = dev.launch_count
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    stats = []
+    barrier()
+    e0.record(stream)
+    for _ in range(args.steps):
+        dev.step_forward(False)
+        stats.append(dev.last_stats.as_dict())
+    e1.record(stream)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = dev.launch_count - launches0
+    clocks = sampler.stop() if rank == 0 else None
+    if world > 1:
+        tms = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        torch.distributed.all_reduce(tms, op=torch.distributed.ReduceOp.MAX)
+        ms = float(tms.item())
+    n_active = stats[-1]["n_active"]
+    value = n_active * args.steps / (ms * 1e-3)
+
+    # roofline of the dominant kernel (pcg_kernel, one launch per step): algorithmic bytes per launch =
+    # I * (12 nnz + 108 n) + 32 n, n = Inner rows, nnz incl. the diagonal
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    else:
+        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    solve_bytes = sum(s["cg_iterations"] * (12.0 * s["nnz"] + 108.0 * s["n_inner"]) + 32.0 * s["n_inner"] for s in stats)
+    solve_ms = sum(s["ms_solve"] for s in stats)
+    achieved = solve_bytes / (solve_ms * 1e-3) / 1e9 if solve_ms > 0 else 0.0
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "pcg_traffic.json")
+    if os.path.exists(tpath):
+        tj = json.load(open(tpath))
+        if tj.get("nx_fluid") == args.nx and world == 1:
+            traffic = tj.get("dram_bytes_per_launch")
+    roofline = {"kernel": "pcg_kernel (persistent Jacobi-PCG, 1 launch per step)", "bound": "hbm",
+                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                "peak_source": peak_src, "bytes_per_launch": solve_bytes / len(stats),
+                "ms_per_launch": solve_ms / len(stats)}
+    mean = lambda k: sum(s[k] for s in stats) / len(stats)  # noqa: E731
+
+    # ---- e2e through the host-buffer C ABI: upload (pinned) -> step -> download, every step ----
+    e2e = None
+    if not args.no_e2e:
+        st = dev.download(["type", "position", "velocity", "pressure"])
+        pin = {k: torch.from_numpy(a).pin_memory() for k, a in st.items()}  # pinned host buffers
+        host = {k: pin[k].numpy() for k in pin}
+        inputs = {k: host[k] for k in ("type", "position", "velocity")}
+        n_e2e = max(1, min(args.steps, args.e2e_steps))
+        h2d = sum(a.nbytes for a in inputs.values())
+        d2h = sum(a.nbytes for a in host.values())
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(n_e2e):
+            dev.upload(inputs)           # H2D of the step's inputs
+            dev.step_forward(False)
+            dev.download_into(host)      # D2H of the step's result (state + pressure) into the same buffers
+        barrier()
+        sec = time.perf_counter() - t0
+        if world > 1:
+            tt = torch.tensor([sec], device="cuda", dtype=torch.float64)
+            torch.distributed.all_reduce(tt, op=torch.distributed.ReduceOp.MAX)
+            sec = float(tt.item())
+        e2e = {"value": dev.last_stats.n_active * n_e2e / sec, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+               "d2h_bytes_per_step": int(d2h), "steps": n_e2e}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        kind, n, times = time_cpu_steps(args.cpu_nx, 3, 0, budget_s=10.0)
+        v_cpu = n * len(times) / sum(times)
+        cpu = {"value": v_cpu, "unit": UNIT, "cores": cpu_threads(), "kind": kind,
+               "sample": cpu_sample_text(args.cpu_nx, n, kind, len(times)),
+               "extrapolated_full_size": v_cpu * (args.cpu_nx / args.nx)}
+
+    if rank == 0:
+        out = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(args.nx, len(t), "1 GPU" if world == 1 else f"{world} y-slabs (PPE rows)"),
+            "ppe_solve_ms_per_step": mean("ms_solve"), "cg_iterations_per_step": mean("cg_iterations"),
+            "us_per_cg_iteration": 1e3 * solve_ms / max(1, sum(s["cg_iterations"] for s in stats)),
+            "phase_ms_per_step": {k[3:]: mean(k) for k in ("ms_neighbors", "ms_explicit", "ms_collision", "ms_assemble",
+                                                           "ms_solve", "ms_correct", "ms_total")},
+            "n_inner": stats[-1]["n_inner"], "nnz": stats[-1]["nnz"],
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+        }
+        print(json.dumps(out), flush=True)
+    dev.close()
+    if world > 1:
+        torch.distributed.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--nx", type=int, default=DEFAULT_NX, help="fluid columns of the scaled dam break (multiple of 8)")
+    ap.add_argument("--cpu-nx", type=int, default=CPU_SAMPLE_NX, help="size of the bounded CPU sample")
+    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference_arm(args)
+    return run_gpu_arm(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

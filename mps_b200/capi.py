@@ -178,6 +178,20 @@ class DeviceMPS:
         self._check(self.lib.mpsb_download(self.h, mask, ct.byref(cf)))
         return arrs
 
+    def download_into(self, arrs):
+        """Download into caller-owned (e.g. pinned) contiguous numpy arrays, keyed by field name."""
+        cf, mask = CFields(), 0
+        for name, dt, w, bit in _FIELD_SPECS:
+            a = arrs.get(name)
+            if a is None:
+                continue
+            if a.dtype != dt or not a.flags.c_contiguous or a.size != self.n * w:
+                raise ValueError(f"download_into: {name} must be C-contiguous {dt.__name__}[{self.n}*{w}]")
+            setattr(cf, name, a.ctypes.data)
+            mask |= bit
+        self._check(self.lib.mpsb_download(self.h, mask, ct.byref(cf)))
+        return arrs
+
     def upload(self, arrs):
         cf, mask, keep = CFields(), 0, []
         for name, dt, w, bit in _FIELD_SPECS:

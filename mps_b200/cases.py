@@ -306,3 +306,61 @@ def scaled_dambreak(nx_fluid: int, base: str = "dambreak_fine"):
     s.input_csv_path = ""
     t, p = generate_lattice(l0, g["domain_x"], g["domain_y"], g["fluid_x"], g["fluid_y"])
     return s, t, p, np.zeros_like(p)
+
+
+def write_settings_yaml(s: Settings, path: str, finish_time=None, output_interval=None):
+    """settings.yml with the reference's exact keys (src/settings.cpp:20-84) for a generated case, so the
+    compiled reference (whose MPS constructor only takes a YAML path) can run the same settings.
+    Ratios are written with repr() so re = ratio*l0 round-trips bit-for-bit where the ratio is exact."""
+    l0 = s.particle_distance
+
+    def ratio(x):
+        r = x / l0
+        for digits in range(1, 17):  # shortest decimal that reproduces x when multiplied back
+            c = float(f"{r:.{digits}g}")
+            if c * l0 == x:
+                return repr(_F(c))
+        return repr(_F(r))
+
+    yn = lambda b: "True" if b else "False"  # noqa: E731
+
+    class _F(float):  # fkYAML reads `1e-06` as a non-float: always write a decimal point in the mantissa
+        def __repr__(self):
+            r = float.__repr__(self)
+            if "e" in r and "." not in r:
+                m, e = r.split("e")
+                r = m + ".0e" + e
+            return r
+    lines = [
+        "dim: %d" % s.dim,
+        "particle distance: %r" % _F(l0),
+        "dt: %r" % _F(s.dt),
+        "finish time: %r" % _F(s.finish_time if finish_time is None else finish_time),
+        "output interval: %r" % _F(s.output_interval if output_interval is None else output_interval),
+        "CFL condition: %r" % _F(s.cfl_condition),
+        "domain range X: [%r, %r]" % (_F(s.domain_min[0]), _F(s.domain_max[0])),
+        "domain range Y: [%r, %r]" % (_F(s.domain_min[1]), _F(s.domain_max[1])),
+        "domain range Z: [%r, %r]" % (_F(s.domain_min[2]), _F(s.domain_max[2])),
+        "density: %r" % _F(s.density),
+        "kinematic viscosity: %r" % _F(s.kinematic_viscosity),
+        "gravity: [%r, %r, %r]" % tuple(_F(g) for g in s.gravity),
+        "effective radius ratio:",
+        "  pressure: %s" % ratio(s.re_pressure),
+        "  viscosity: %s" % ratio(s.re_viscosity),
+        "  surface detection: %s" % ratio(s.re_surface),
+        "threshold for surface detection: %r" % _F(s.surface_threshold),
+        "pressure stabilization:",
+        "  quasi compressibility:",
+        "    on: %s" % yn(s.quasi_compressibility_on),
+        "    compressibility: %r" % _F(s.compressibility if s.quasi_compressibility_on else 0.0),
+        "  higher order source term:",
+        "    on: %s" % yn(s.higher_order_source_on),
+        "    gamma: %r" % _F(s.higher_order_gamma if s.higher_order_source_on else 0.0),
+        "relaxation coefficient for pressure: %r" % _F(s.relaxation_coefficient),
+        "collision distance ratio: %s" % ratio(s.collision_distance),
+        "coefficient of restitution: %r" % _F(s.restitution),
+        "inputCsvPath: %s" % (s.input_csv_path or "none.csv"),
+    ]
+    with open(path, "w") as f:
+        f.write("\n".join(lines) + "\n")
+    return path
