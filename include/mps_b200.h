@@ -185,6 +185,12 @@ int mpsb_upload_device(mpsb_handle* h, const int32_t* d_type, const double* d_po
 /* Run all subsequent work of this handle on the caller's CUDA stream (a cudaStream_t passed as
  * void*; NULL restores the handle's own stream), so the host can bracket steps with its own events. */
 int mpsb_set_stream(mpsb_handle* h, void* cuda_stream);
+/* Diagnostic: SM cycles CTA 0 spent in the last solve's sweep A (SpMV), sweep B, sweep C, and in the
+ * reductions + grid barriers (4 values). */
+int mpsb_debug_cg_cycles(const mpsb_handle* h, int64_t* out4);
+/* Diagnostic: the same four counters for every CTA of the last solve plus its SM id, as 5 rows of
+ * *nblocks int64 (row-major: A, B, C, sync, smid). */
+int mpsb_debug_cg_block_cycles(mpsb_handle* h, int64_t* out, int capacity_blocks, int* nblocks);
 /* Counters since create: kernel launches issued by this library on this handle. */
 int64_t mpsb_launch_count(const mpsb_handle* h);
 

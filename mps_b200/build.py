@@ -28,7 +28,13 @@ def _newer(target, sources):
     return any(os.path.getmtime(s) > t for s in sources)
 
 
-def build_library(force=False, verbose=False):
+def build_library(force=False, verbose=False, out=None, extra=()):
+    """out / extra: experiment builds (tools/): another file name and extra -D flags."""
+    if out is not None:
+        srcs = sorted(glob.glob(os.path.join(HERE, "csrc", "*.cu")))
+        nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+        subprocess.run([nvcc] + NVCC_FLAGS + list(extra) + ["-o", out] + srcs, check=True)
+        return out
     srcs = sorted(glob.glob(os.path.join(HERE, "csrc", "*.cu")))
     deps = srcs + glob.glob(os.path.join(HERE, "csrc", "*.cuh")) + [os.path.join(ROOT, "include", "mps_b200.h")]
     if not force and not _newer(LIB, deps):

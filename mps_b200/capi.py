@@ -15,7 +15,7 @@ import numpy as np
 from .cases import CSettings, Settings
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libmps_b200.so")
+LIB_PATH = os.environ.get("MPSB_LIB_PATH") or os.path.join(HERE, "libmps_b200.so")  # override: experiment builds
 
 (PH_NEIGHBORS, PH_EXPLICIT, PH_COLLISION, PH_FLAGS_SOURCE, PH_MATRIX, PH_DIRICHLET, PH_SOLVE, PH_PRESSURE_POST,
  PH_GRADIENT_MOVE, PH_NUMBER_DENSITY, PH_COURANT) = range(11)
@@ -27,6 +27,7 @@ EXPORTED = [
     "mpsb_create", "mpsb_destroy", "mpsb_last_error", "mpsb_version", "mpsb_step", "mpsb_run_phase",
     "mpsb_upload", "mpsb_download", "mpsb_num_particles", "mpsb_get_neighbors", "mpsb_get_ppe", "mpsb_events",
     "mpsb_comm_unique_id", "mpsb_attach_comm", "mpsb_upload_device", "mpsb_launch_count", "mpsb_set_stream",
+    "mpsb_debug_cg_cycles", "mpsb_debug_cg_block_cycles",
 ]
 
 
@@ -234,6 +235,22 @@ class DeviceMPS:
     def set_stream(self, cuda_stream_ptr):
         """Run on the caller's CUDA stream (e.g. torch.cuda.current_stream().cuda_stream)."""
         self._check(self.lib.mpsb_set_stream(self.h, ct.c_void_p(cuda_stream_ptr)))
+
+    def cg_cycles(self):
+        out = (ct.c_int64 * 4)()
+        self.lib.mpsb_debug_cg_cycles.argtypes = [ct.c_void_p, ct.c_void_p]
+        self._check(self.lib.mpsb_debug_cg_cycles(self.h, out))
+        return list(out)
+
+    def cg_block_cycles(self):
+        """(5, nblocks) int64: per-CTA cycles in sweep A, B, C, reductions+barriers, and the SM id."""
+        cap = 1024
+        out = np.zeros((5, cap), dtype=np.int64)
+        nb = ct.c_int()
+        self.lib.mpsb_debug_cg_block_cycles.argtypes = [ct.c_void_p, ct.c_void_p, ct.c_int, ct.POINTER(ct.c_int)]
+        flat = np.zeros(5 * cap, dtype=np.int64)
+        self._check(self.lib.mpsb_debug_cg_block_cycles(self.h, flat.ctypes.data, cap, ct.byref(nb)))
+        return flat[:5 * nb.value].reshape(5, nb.value)
 
     @property
     def launch_count(self):

@@ -38,13 +38,12 @@ __global__ void __launch_bounds__(256) explicit_kernel(Params P) {
     double u = P.S.u[s], v = P.S.v[s], w = P.S.w[s];
     if (s < *P.n_active && P.S.type[s] == MPSB_FLUID) {
         const double re = P.s.re_viscosity;
-        const size_t N  = (size_t) P.N;
         int cnt = P.nbr_count[s];
         double tx = 0.0, ty = 0.0, tz = 0.0;
         for (int k = 0; k < cnt; k++) {
-            double d = P.nbr_dist[k * N + s];
+            double d = P.nbr_dist[SELL(k, s)];
             if (d < re) {
-                int j      = P.nbr_idx[k * N + s];
+                int j      = P.nbr_idx[SELL(k, s)];
                 double wgt = (re / d) - 1.0;
                 tx += (P.S.u[j] - u) * wgt;
                 ty += (P.S.v[j] - v) * wgt;
@@ -76,12 +75,11 @@ __global__ void __launch_bounds__(256) explicit_kernel(Params P) {
 __global__ void __launch_bounds__(256) collision_candidates_kernel(Params P) {
     int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= *P.n_active || P.S.type[s] != MPSB_FLUID) return;
-    const size_t N = (size_t) P.N;
     int cnt = P.nbr_count[s], id = P.S.id[s];
     for (int k = 0; k < cnt; k++) {
-        double d = P.nbr_dist[k * N + s];
+        double d = P.nbr_dist[SELL(k, s)];
         if (d < P.s.collision_distance) {
-            int j = P.nbr_idx[k * N + s];
+            int j = P.nbr_idx[SELL(k, s)];
             if (P.S.type[j] == MPSB_FLUID && P.S.id[j] >= id) continue;
             int c = atomicAdd(P.cand_count, 1);
             if (c < P.cand_cap)
@@ -115,13 +113,12 @@ __global__ void __launch_bounds__(1024) collision_replay_kernel(Params P) {
             __syncthreads();
         }
     if (threadIdx.x != 0) return;
-    const size_t N   = (size_t) P.N;
     const double col = P.s.collision_distance, e = P.s.restitution;
     for (int c = 0; c < M; c++) {
         unsigned long long key = P.cand[c];
         int s = P.H.inv[(int) (key >> 32)], k = (int) (key & 0xffffffffu);
-        int j = P.nbr_idx[k * N + s];
-        double dist = P.nbr_dist[k * N + s];
+        int j = P.nbr_idx[SELL(k, s)];
+        double dist = P.nbr_dist[SELL(k, s)];
         double invMi = P.inv_density;                                       // i is Fluid
         double invMj = P.S.type[j] == MPSB_FLUID ? P.inv_density : 0.0;    // src/particle.cpp:19-29
         double reducedMass = 1.0 / (invMi + invMj);
@@ -153,14 +150,13 @@ __global__ void __launch_bounds__(256) gradient_kernel(Params P) {
     int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= *P.n_active || P.S.type[s] != MPSB_FLUID) return;
     const double re = P.s.re_pressure;
-    const size_t N  = (size_t) P.N;
     const double xi = P.S.x[s], yi = P.S.y[s], zi = P.S.z[s], pmin = P.S.minp[s];
     int cnt = P.nbr_count[s];
     double gx = 0.0, gy = 0.0, gz = 0.0;
     for (int k = 0; k < cnt; k++) {
-        double d = P.nbr_dist[k * N + s];
+        double d = P.nbr_dist[SELL(k, s)];
         if (d < re) {
-            int j = P.nbr_idx[k * N + s];
+            int j = P.nbr_idx[SELL(k, s)];
             if (P.S.type[j] == MPSB_DUMMY_WALL) continue;
             double dp = P.S.p[j] - pmin, wgt = (re / d) - 1.0, d2 = d * d;
             gx += (P.S.x[j] - xi) * dp * wgt / d2;

@@ -25,7 +25,6 @@ __global__ void __launch_bounds__(128) neighbor_kernel(Params P) {
     int iz = key / nxy, rem = key - iz * nxy;
     int iy = rem / P.numX, ix = rem - iy * P.numX;
     int count = 0;
-    const size_t N = (size_t) P.N;
     for (int jx = ix - 1; jx <= ix + 1; jx++) {
         if (jx < 0 || jx >= P.numX) continue;
         for (int jy = iy - 1; jy <= iy + 1; jy++) {
@@ -39,8 +38,8 @@ __global__ void __launch_bounds__(128) neighbor_kernel(Params P) {
                     double dist = sqrt((dx * dx + dy * dy) + dz * dz); // Eigen (pj - pi).norm()
                     if (j != s && dist < re) {
                         if (count < P.K) {
-                            P.nbr_idx[count * N + s]  = j;
-                            P.nbr_dist[count * N + s] = dist;
+                            P.nbr_idx[SELL(count, s)]  = j;
+                            P.nbr_dist[SELL(count, s)] = dist;
                         }
                         count++;
                     }
@@ -67,11 +66,10 @@ __global__ void number_density_kernel(Params P) {
     double ratio = 0.0;
     if (P.S.bc[s] != MPSB_BC_SURFACE) {
         const double re = P.s.re_pressure;
-        const size_t N  = (size_t) P.N;
         int cnt = P.nbr_count[s];
         double n = 0.0;
         for (int k = 0; k < cnt; k++) {
-            double d = P.nbr_dist[k * N + s];
+            double d = P.nbr_dist[SELL(k, s)];
             if (d < re) n += mpsb_weight(d, re);
         }
         ratio = n / P.s.n0_pressure;

@@ -1,7 +1,6 @@
 // k_pcg.cu — the pressure Poisson solve: Jacobi-preconditioned conjugate gradient as ONE persistent
-// cooperative kernel (one launch per solve; grid-wide barriers between the three sweeps of an
-// iteration; no host round trips, so the small shipped cases are not launch-bound and the 4 M case
-// streams the matrix at HBM rate).
+// cooperative kernel (one launch per solve, one CTA per SM; grid-wide barriers between the three
+// sweeps of an iteration; no host round trips).
 //
 // Replaces reference MPS::solvePoissonEquation (src/mps.cpp:417-470), i.e. Eigen 3.4.0
 // ConjugateGradient<SparseMatrix<double>, Lower, DiagonalPreconditioner> with all defaults:
@@ -12,24 +11,85 @@
 // The reference solves twice with identical input (:457,:460); once is enough (SURVEY B-4).
 // Iteration numbering follows Eigen: `iterations()` is the loop counter at exit.
 //
-// Per iteration, over n rows with ELL off-diagonals (fp64 value + int32 column):
-//   sweep A  ap = A p, partial p.ap            12 B per stored entry + 4n (count) + 8n diag + 8n p + 8n ap
-//   sweep B  x += a p; r -= a ap; |r|^2, r.z   read x,p,r,ap,invdiag, write x,r = 56n
+// Per iteration, over n rows with sliced-ELL off-diagonals (fp64 value + int32 column):
+//   sweep A  ap = A p, partial p.ap     the matrix streams HBM -> shared memory through 1-D TMA bulk
+//                                       copies (cp.async.bulk + mbarrier), one ring of stages per warp,
+//                                       so the bytes in flight do not depend on registers/occupancy;
+//                                       p[col] gathers are served by L1/L2 (p is 8n bytes, L2-resident)
+//   sweep B  x += a p; r -= a ap; |r|^2, r.z   read x,p,r,ap,invdiag, write x,r = 56n   (16-byte vectors)
 //   sweep C  p = z + b p (z = invdiag r)       read r,invdiag,p, write p = 32n
 // = 12 nnz + 108 n algorithmic bytes, the figure bench.py's roofline uses.
 #include "mpsb_internal.cuh"
 
 #include <cfloat>
+#include <cstdlib>
 #include <cooperative_groups.h>
 
 namespace cg = cooperative_groups;
 
+#ifndef PCG_EXP
+#define PCG_EXP 0
+#endif
+
 namespace {
 
-constexpr int PCG_THREADS = 256;
+constexpr int PCG_WARPS   = 16;            // warps per CTA (one CTA per SM)
+constexpr int PCG_THREADS = PCG_WARPS * 32;
+constexpr int PCG_STAGES  = 3;             // ring depth per warp
+constexpr int PCG_CH      = 8;             // slots per stage (multiple of 4): 8 * 384 B = 3 KB + diag
+// one stage: CH slots of 32 values, the slice's 32 diagonals, CH slots of 32 columns
+struct __align__(128) Stage {
+    double val[PCG_CH * 32];
+    double diag[32];
+    int col[PCG_CH * 32];
+};
+struct __align__(16) StageMeta {
+    int slice;
+    int nslots;
+    int first; // first chunk of the slice (start the row sum from diag * p)
+    int last;  // last chunk of the slice (store ap, accumulate p.ap)
+};
+struct Smem {
+    Stage stage[PCG_WARPS][PCG_STAGES];
+    StageMeta meta[PCG_WARPS][PCG_STAGES];
+    unsigned long long full[PCG_WARPS][PCG_STAGES];
+    double red[66];
+};
 
-// Deterministic block-wide sum of up to two values; result broadcast to every thread.
-__device__ __forceinline__ void block_sum2(double& a, double& b, double* sh /* 2*32 + 2 */) {
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned) __cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(unsigned long long* bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned long long* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
+    unsigned ok = 0, addr = smem_u32(bar), spins = 0;
+    while (!ok) {
+        if (++spins > (1u << 26)) __trap(); // a lost TMA completion must fail loudly, never hang the GPU
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok)
+            : "r"(addr), "r"(parity)
+            : "memory");
+    }
+}
+// 1-D TMA bulk copy global -> shared, completion counted in bytes on an mbarrier
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, unsigned long long* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+// Deterministic block-wide sum of two values; result broadcast to every thread.
+__device__ __forceinline__ void block_sum2(double& a, double& b, double* sh /* 66 */) {
     int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -43,8 +103,7 @@ __device__ __forceinline__ void block_sum2(double& a, double& b, double* sh /* 2
     }
     __syncthreads();
     if (warp == 0) {
-        constexpr int W = PCG_THREADS / 32;
-        double va = lane < W ? sh[lane] : 0.0, vb = lane < W ? sh[32 + lane] : 0.0;
+        double va = lane < PCG_WARPS ? sh[lane] : 0.0, vb = lane < PCG_WARPS ? sh[32 + lane] : 0.0;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             va += __shfl_xor_sync(0xffffffffu, va, o);
@@ -73,39 +132,149 @@ __device__ __forceinline__ void grid_sum2(const double* pa, const double* pb, in
     b = lb;
 }
 
-__global__ void __launch_bounds__(PCG_THREADS) pcg_kernel(Params P, int max_blocks, int iteration_cap) {
+// Ring bookkeeping of one warp; serial numbers keep running across sweeps so the mbarrier phase
+// parity of stage (serial % STAGES) is (serial / STAGES) & 1.
+struct Pipe {
+    unsigned issued;
+    unsigned consumed;
+};
+
+constexpr int PCG_BATCH = 2; // slices taken from the global queue per atomic
+
+// Sweep A for the calling warp: ap = A p. Slices are handed out DYNAMICALLY (a global ticket counter,
+// PCG_BATCH slices per ticket, tickets fetched two ahead so neither the atomic nor the width loads sit
+// on the critical path): a static split leaves fast warps idle while HBM serves the slow ones, which
+// cost 25 % of the sweep. Determinism is kept by storing p.ap PER SLICE (warp-reduced in a fixed order)
+// into slice_pap[]; the caller sums that array in a fixed order. Rows of a slice beyond n carry diag 0 /
+// padding only and p = 0 there.
+__device__ __forceinline__ void spmv_sweep(const Params& P, Smem& sm, Pipe& pipe, int n, const double* p, double* ap,
+                                           unsigned* ticket, double* slice_pap) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int nslices = (n + 31) >> 5;
+    const size_t K    = (size_t) P.K;
+    auto take = [&]() -> int { // lane 0 holds the result; shuffled when needed
+        int v = 0;
+        if (lane == 0) v = (int) atomicAdd(ticket, (unsigned) PCG_BATCH);
+        return v;
+    };
+    auto widths = [&](int s0) -> int { return (lane < PCG_BATCH && s0 + lane < nslices) ? P.ell_width[s0 + lane] : 0; };
+    // batch pipeline: cur (being issued), nxt (id known, widths loading), t2 (ticket in flight)
+    int cur = __shfl_sync(0xffffffffu, take(), 0);
+    int cur_w = widths(cur);
+    int nxt = __shfl_sync(0xffffffffu, take(), 0);
+    int nxt_w = widths(nxt);
+    int t2 = take();
+    int pi = 0, pk = 0; // producer cursor: slice index inside cur, slot offset
+    int pw = __shfl_sync(0xffffffffu, cur_w, 0);
+    auto produce = [&]() -> bool {
+        if (cur + pi >= nslices || pipe.issued - pipe.consumed >= (unsigned) PCG_STAGES) return false;
+        const int slice = cur + pi;
+        const int nsl   = min(PCG_CH, pw - pk);
+        const bool first = pk == 0, last = pk + nsl >= pw;
+        const unsigned st = pipe.issued % PCG_STAGES;
+        if (lane == 0) {
+            Stage& S = sm.stage[warp][st];
+            sm.meta[warp][st] = StageMeta{slice, nsl, first ? 1 : 0, last ? 1 : 0};
+            unsigned long long* bar = &sm.full[warp][st];
+            mbar_arrive_expect_tx(bar, (first ? 256u : 0u) + (unsigned) nsl * 384u);
+            if (first) bulk_g2s(S.diag, P.diag + (size_t) slice * 32, 256u, bar);
+            if (nsl > 0) {
+                const size_t off = ((size_t) slice * K + (size_t) pk) * 32;
+                bulk_g2s(S.val, P.ell_val + off, (unsigned) nsl * 256u, bar);
+                bulk_g2s(S.col, P.ell_col + off, (unsigned) nsl * 128u, bar);
+            }
+        }
+        pipe.issued++;
+        pk += nsl;
+        if (last) {
+            pk = 0;
+            if (++pi == PCG_BATCH) { // next batch; keep two tickets ahead
+                pi = 0;
+                cur = nxt; cur_w = nxt_w;
+                nxt = __shfl_sync(0xffffffffu, t2, 0);
+                nxt_w = widths(nxt);
+                t2 = nxt < nslices ? take() : nslices;
+            }
+            pw = __shfl_sync(0xffffffffu, cur_w, pi);
+        }
+        return true;
+    };
+    double sum = 0.0, pr = 0.0;
+    int row = 0;
+    for (;;) {
+        while (produce()) {}
+        if (pipe.consumed == pipe.issued) break;
+        __syncwarp(); // lane 0's meta of freshly issued stages is visible to the warp
+        const unsigned st = pipe.consumed % PCG_STAGES, parity = (pipe.consumed / PCG_STAGES) & 1u;
+        const StageMeta m = sm.meta[warp][st];
+        const Stage& S    = sm.stage[warp][st];
+        if (m.first) { // own-row p: issued before the wait so its latency hides behind the TMA
+            row = m.slice * 32 + lane;
+            pr  = p[row];
+        }
+        mbar_wait(&sm.full[warp][st], parity);
+        if (m.first) sum = S.diag[lane] * pr;
+#pragma unroll
+        for (int k = 0; k < PCG_CH; k += 4) {
+            if (k < m.nslots) {
+                int c0 = S.col[(k + 0) * 32 + lane], c1 = S.col[(k + 1) * 32 + lane];
+                int c2 = S.col[(k + 2) * 32 + lane], c3 = S.col[(k + 3) * 32 + lane];
+                double p0 = p[c0], p1 = p[c1], p2 = p[c2], p3 = p[c3];
+                double v0 = S.val[(k + 0) * 32 + lane], v1 = S.val[(k + 1) * 32 + lane];
+                double v2 = S.val[(k + 2) * 32 + lane], v3 = S.val[(k + 3) * 32 + lane];
+                sum += v0 * p0; sum += v1 * p1; sum += v2 * p2; sum += v3 * p3;
+            }
+        }
+        if (m.last) {
+            ap[row] = sum;
+            double v = pr * sum;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            if (lane == 0) slice_pap[m.slice] = v;
+        }
+        __syncwarp(); // every lane is done with the stage before lane 0 refills it
+        pipe.consumed++;
+    }
+}
+
+__global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_blocks, int iteration_cap) {
     cg::grid_group grid = cg::this_grid();
-    __shared__ double sh[66];
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    Smem& sm = *reinterpret_cast<Smem*>(smem_raw);
+    double* sh = sm.red;
     const int n       = *P.n_active;
     const int nblocks = gridDim.x;
     const int tid     = blockIdx.x * PCG_THREADS + threadIdx.x;
     const int stride  = nblocks * PCG_THREADS;
-    const size_t N    = (size_t) P.N;
-    double* __restrict__ x  = P.S.p;
-    double* __restrict__ r  = P.cg_r;
-    double* __restrict__ p  = P.cg_p;
-    double* __restrict__ ap = P.cg_ap;
-    double* __restrict__ invd = P.cg_invdiag;
-    const double* __restrict__ diag = P.diag;
-    const double* __restrict__ ell_val = P.ell_val;
-    const int* __restrict__ ell_col = P.ell_col;
-    const int* __restrict__ ell_count = P.ell_count;
+    double* x    = P.S.p;
+    double* r    = P.cg_r;
+    double* p    = P.cg_p; // deliberately not __restrict__/const: gathers must be coherent ld.global
+    double* ap   = P.cg_ap;
+    double* invd = P.cg_invdiag;
     double* part0 = P.cg_partials;
     double* part1 = part0 + max_blocks;
     double* part2 = part1 + max_blocks;
+    unsigned* tickets = reinterpret_cast<unsigned*>(P.cg_partials + 8 * (size_t) max_blocks); // 2 slice queues
 
-    // setup: x = 0, r = b, invdiag, p = invdiag r; |b|^2 and r.p
+    if (threadIdx.x < PCG_WARPS * PCG_STAGES) mbar_init(&sm.full[0][0] + threadIdx.x, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    __syncthreads();
+    Pipe pipe{0u, 0u};
+
+    // setup: x = 0, r = b, invdiag, p = invdiag r (0 beyond n, up to the slice padding); |b|^2 and r.p
     double l0 = 0.0, l1 = 0.0;
-    for (int i = tid; i < P.N; i += stride) {
-        x[i] = 0.0;
+    for (int i = tid; i < P.Np; i += stride) {
+        if (i < P.N) x[i] = 0.0;
+        double pi = 0.0;
         if (i < n) {
-            double bi = P.rhs[i], d = diag[i];
+            double bi = P.rhs[i], d = P.diag[i];
             double id = d != 0.0 ? 1.0 / d : 1.0;
-            double pi = id * bi;
-            r[i] = bi; invd[i] = id; p[i] = pi;
+            pi = id * bi;
+            r[i] = bi; invd[i] = id;
             l0 += bi * bi;
             l1 += bi * pi;
         }
+        p[i] = pi;
     }
     block_sum2(l0, l1, sh);
     if (threadIdx.x == 0) {
@@ -126,26 +295,26 @@ __global__ void __launch_bounds__(PCG_THREADS) pcg_kernel(Params P, int max_bloc
     if (!done && residualNorm2 < threshold) done = true;
     grid.sync(); // part0/part1 are reused below
     const int maxIters = iteration_cap > 0 ? iteration_cap : 2 * P.N;
+    const int npairs = n >> 1;
 
+    long long cyc[4] = {0, 0, 0, 0}, t0 = clock64(), t1;
+#define PCG_TICK(slot) do { t1 = clock64(); cyc[slot] += t1 - t0; t0 = t1; } while (0)
     while (!done && it < maxIters) {
         // ---- sweep A: ap = A p, p.ap ----
+        unsigned* ticket = tickets + (it & 1);
+#if !(PCG_EXP == 11 || PCG_EXP == 12)
+        spmv_sweep(P, sm, pipe, n, p, ap, ticket, P.cg_slice_pap);
+#endif
+        __syncthreads();
+        PCG_TICK(0);
+        grid.sync();
+        // p.ap = sum of the per-slice partials in a fixed order: this CTA's fixed range, then all CTAs
+        if (tid == 0) tickets[(it + 1) & 1] = 0u; // the other counter is idle until the next sweep A
         double lpap = 0.0, dummy = 0.0;
-        for (int row = tid; row < n; row += stride) {
-            int cnt    = ell_count[row];
-            double pr  = p[row];
-            double sum = diag[row] * pr;
-            int k = 0;
-            for (; k + 4 <= cnt; k += 4) {
-                int c0 = ell_col[(k + 0) * N + row], c1 = ell_col[(k + 1) * N + row];
-                int c2 = ell_col[(k + 2) * N + row], c3 = ell_col[(k + 3) * N + row];
-                double v0 = ell_val[(k + 0) * N + row], v1 = ell_val[(k + 1) * N + row];
-                double v2 = ell_val[(k + 2) * N + row], v3 = ell_val[(k + 3) * N + row];
-                double p0 = p[c0], p1 = p[c1], p2 = p[c2], p3 = p[c3];
-                sum += v0 * p0; sum += v1 * p1; sum += v2 * p2; sum += v3 * p3;
-            }
-            for (; k < cnt; k++) sum += ell_val[k * N + row] * p[ell_col[k * N + row]];
-            ap[row] = sum;
-            lpap += pr * sum;
+        {
+            const int nslices = (n + 31) >> 5, per = (nslices + nblocks - 1) / nblocks;
+            const int lo = blockIdx.x * per, hi = min(lo + per, nslices);
+            for (int i = lo + (int) threadIdx.x; i < hi; i += PCG_THREADS) lpap += __ldcg(P.cg_slice_pap + i);
         }
         block_sum2(lpap, dummy, sh);
         if (threadIdx.x == 0) part0[blockIdx.x] = lpap;
@@ -153,16 +322,30 @@ __global__ void __launch_bounds__(PCG_THREADS) pcg_kernel(Params P, int max_bloc
         double pap, unused;
         grid_sum2(part0, part0, nblocks, pap, unused, sh);
         const double alpha = absNew / pap;
-        // ---- sweep B: x += alpha p; r -= alpha ap; |r|^2; r.z ----
+        PCG_TICK(3);
+        // ---- sweep B: x += alpha p; r -= alpha ap; |r|^2; r.z  (two rows per thread, 16-byte accesses) ----
         double lrr = 0.0, lrz = 0.0;
-        for (int i = tid; i < n; i += stride) {
-            double pi = p[i], ri = r[i], api = ap[i], idg = invd[i];
-            x[i] += alpha * pi;
-            ri -= alpha * api;
+#pragma unroll 2
+        for (int i = tid; i < (PCG_EXP == 10 || PCG_EXP == 12 ? 0 : npairs); i += stride) {
+            double2 pp = reinterpret_cast<const double2*>(p)[i], rr = reinterpret_cast<const double2*>(r)[i];
+            double2 aa = reinterpret_cast<const double2*>(ap)[i], dd = reinterpret_cast<const double2*>(invd)[i];
+            double2 xx = reinterpret_cast<const double2*>(x)[i];
+            xx.x += alpha * pp.x; xx.y += alpha * pp.y;
+            rr.x -= alpha * aa.x; rr.y -= alpha * aa.y;
+            reinterpret_cast<double2*>(x)[i] = xx;
+            reinterpret_cast<double2*>(r)[i] = rr;
+            lrr += rr.x * rr.x; lrr += rr.y * rr.y;
+            lrz += rr.x * (dd.x * rr.x); lrz += rr.y * (dd.y * rr.y);
+        }
+        if ((n & 1) && tid == 0) {
+            int i = n - 1;
+            double ri = r[i] - alpha * ap[i];
+            x[i] += alpha * p[i];
             r[i] = ri;
             lrr += ri * ri;
-            lrz += ri * (idg * ri);
+            lrz += ri * (invd[i] * ri);
         }
+        PCG_TICK(1);
         block_sum2(lrr, lrz, sh);
         if (threadIdx.x == 0) {
             part1[blockIdx.x] = lrr;
@@ -171,15 +354,34 @@ __global__ void __launch_bounds__(PCG_THREADS) pcg_kernel(Params P, int max_bloc
         grid.sync();
         double rz;
         grid_sum2(part1, part2, nblocks, residualNorm2, rz, sh);
-        if (residualNorm2 < threshold) break;
+        if (PCG_EXP < 10 && residualNorm2 < threshold) break;
         const double beta = rz / absNew;
         absNew = rz;
+        PCG_TICK(3);
         // ---- sweep C: p = z + beta p ----
-        for (int i = tid; i < n; i += stride) p[i] = invd[i] * r[i] + beta * p[i];
+#pragma unroll 2
+        for (int i = tid; i < (PCG_EXP == 10 || PCG_EXP == 12 ? 0 : npairs); i += stride) {
+            double2 pp = reinterpret_cast<const double2*>(p)[i], rr = reinterpret_cast<const double2*>(r)[i];
+            double2 dd = reinterpret_cast<const double2*>(invd)[i];
+            pp.x = dd.x * rr.x + beta * pp.x;
+            pp.y = dd.y * rr.y + beta * pp.y;
+            reinterpret_cast<double2*>(p)[i] = pp;
+        }
+        if ((n & 1) && tid == 0) p[n - 1] = invd[n - 1] * r[n - 1] + beta * p[n - 1];
         it++;
+        PCG_TICK(2);
         grid.sync();
+        PCG_TICK(3);
+    }
+    if (threadIdx.x == 0) { // per-CTA diagnostic rows behind the three reduction rows
+        long long* dbg = reinterpret_cast<long long*>(P.cg_partials + 3 * (size_t) max_blocks);
+        for (int k = 0; k < 4; k++) dbg[(size_t) k * max_blocks + blockIdx.x] = cyc[k];
+        unsigned smid;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        dbg[(size_t) 4 * max_blocks + blockIdx.x] = smid;
     }
     if (tid == 0) {
+        for (int k = 0; k < 4; k++) P.stats->cg_cycles[k] = cyc[k];
         P.stats->cg_iterations   = it;
         P.stats->rhs_norm2       = rhsNorm2;
         P.stats->cg_rel_residual = rhsNorm2 > 0.0 ? sqrt(residualNorm2 / rhsNorm2) : 0.0;
@@ -189,23 +391,30 @@ __global__ void __launch_bounds__(PCG_THREADS) pcg_kernel(Params P, int max_bloc
 } // namespace
 
 int mpsb_pcg_configure(mpsb_handle* h) {
+    int smem = (int) sizeof(Smem);
+    if (cudaFuncSetAttribute(pcg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return -1;
     int per_sm = 0;
-    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, pcg_kernel, PCG_THREADS, 0);
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, pcg_kernel, PCG_THREADS, smem);
     if (e != cudaSuccess || per_sm < 1) return -1;
     h->cg_threads    = PCG_THREADS;
-    h->cg_max_blocks = per_sm * h->num_sms;
+    h->cg_smem       = smem;
+    h->cg_max_blocks = h->num_sms; // one CTA per SM
+    const char* cap  = getenv("MPSB_CG_ITERATION_CAP"); // diagnostic (profiling a bounded solve); 0 = Eigen's 2N
+    h->cg_iteration_cap = cap ? atoi(cap) : 0;
     return 0;
 }
 
 void mpsb_launch_pcg(mpsb_handle* h) {
     Params& P = h->P;
-    // enough CTAs to cover the rows, never more than can be co-resident (cooperative launch)
-    int want = mpsb_div_up(P.N, PCG_THREADS);
+    // one 32-row slice per warp at least; never more CTAs than can be co-resident (cooperative launch)
+    int want = mpsb_div_up(P.Np / 32, PCG_WARPS);
     int grid = want < h->cg_max_blocks ? want : h->cg_max_blocks;
     if (grid < 1) grid = 1;
     int max_blocks = h->cg_max_blocks;
-    int cap = 0;
+    cudaMemsetAsync(P.cg_partials + 8 * (size_t) max_blocks, 0, 8, h->stream); // the two slice-queue counters
+    int cap = h->cg_iteration_cap;
     void* args[] = {(void*) &P, (void*) &max_blocks, (void*) &cap};
-    cudaLaunchCooperativeKernel((const void*) pcg_kernel, dim3(grid), dim3(PCG_THREADS), args, 0, h->stream);
+    cudaLaunchCooperativeKernel((const void*) pcg_kernel, dim3(grid), dim3(PCG_THREADS), args, (size_t) h->cg_smem,
+                                h->stream);
     h->launches++;
 }

@@ -18,11 +18,10 @@ __global__ void __launch_bounds__(256) flags_kernel(Params P) {
         int type = P.S.type[s];
         if (type != MPSB_GHOST && type != MPSB_DUMMY_WALL) {
             const double re_s = P.s.re_surface, re_p = P.s.re_pressure;
-            const size_t N = (size_t) P.N;
             int cnt = P.nbr_count[s];
             double ns = 0.0, np = 0.0;
             for (int k = 0; k < cnt; k++) {
-                double d = P.nbr_dist[k * N + s];
+                double d = P.nbr_dist[SELL(k, s)];
                 if (d < re_s) ns += (re_s / d) - 1.0;
                 if (d < re_p) np += (re_p / d) - 1.0;
             }
@@ -46,15 +45,14 @@ __global__ void __launch_bounds__(256) source_ho_kernel(Params P) {
     int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= *P.n_active || P.S.bc[s] != MPSB_BC_INNER) return;
     const double re = P.s.re_pressure;
-    const size_t N  = (size_t) P.N;
     const double xi = P.S.x[s], yi = P.S.y[s], zi = P.S.z[s];
     const double ui = P.S.u[s], vi = P.S.v[s], wi = P.S.w[s];
     double b = P.src_ho0 * (P.S.ratio[s] - 1.0);
     int cnt = P.nbr_count[s];
     for (int k = 0; k < cnt; k++) {
-        int j = P.nbr_idx[k * N + s];
+        int j = P.nbr_idx[SELL(k, s)];
         if (P.S.bc[j] == MPSB_BC_IGNORED) continue;
-        double d = P.nbr_dist[k * N + s];
+        double d = P.nbr_dist[SELL(k, s)];
         if (d < re) {
             double rx = P.S.x[j] - xi, ry = P.S.y[j] - yi, rz = P.S.z[j] - zi;
             double ux = P.S.u[j] - ui, uy = P.S.v[j] - vi, uz = P.S.w[j] - wi;
@@ -65,28 +63,31 @@ __global__ void __launch_bounds__(256) source_ho_kernel(Params P) {
     P.rhs[s] = b;
 }
 
-// Row s of the PPE: diagonal kept apart, off-diagonals (Inner-Inner only) compacted into ELL slots.
-// a = (2D/(lambda n0)) * w / rho (src/mps.cpp:343); Surface neighbours add to the diagonal only.
+// Row s of the PPE: diagonal kept apart, off-diagonals (Inner-Inner only) compacted into the slots of
+// the row's 32-row slice. a = (2D/(lambda n0)) * w / rho (src/mps.cpp:343); Surface neighbours add to the
+// diagonal only. Every slice is padded to a common width (the longest row of the slice, rounded up to a
+// multiple of 4) with entries (column = own row, value = +0.0) so the PCG kernel streams whole slices
+// without per-row trip counts; adding +0.0 * p never changes a finite sum. One warp = one slice, so
+// the grid covers Np rows and no thread exits before the warp-wide maximum.
 __global__ void __launch_bounds__(256) matrix_kernel(Params P) {
     int s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= P.N) return;
+    if (s >= P.Np) return; // Np is a multiple of 32: whole warps leave together
     int m = 0;
     double diag = 0.0;
     if (s < *P.n_active && P.S.bc[s] == MPSB_BC_INNER) {
         const double re = P.s.re_pressure;
-        const size_t N  = (size_t) P.N;
         int cnt = P.nbr_count[s];
         for (int k = 0; k < cnt; k++) {
-            double d = P.nbr_dist[k * N + s];
+            double d = P.nbr_dist[SELL(k, s)];
             if (d < re) {
-                int j   = P.nbr_idx[k * N + s];
+                int j   = P.nbr_idx[SELL(k, s)];
                 int bcj = P.S.bc[j];
                 if (bcj == MPSB_BC_IGNORED) continue;
                 double a = P.mat_coef * ((re / d) - 1.0) / P.s.density;
                 diag += a;
                 if (bcj == MPSB_BC_INNER) {
-                    P.ell_col[m * N + s] = j;
-                    P.ell_val[m * N + s] = -a;
+                    P.ell_col[SELL(m, s)] = j;
+                    P.ell_val[SELL(m, s)] = -a;
                     m++;
                 }
             }
@@ -94,6 +95,15 @@ __global__ void __launch_bounds__(256) matrix_kernel(Params P) {
         if (P.s.quasi_compressibility_on) diag += P.qc_term;
         atomicAdd(&P.stats->nnz, m + 1);
     }
+    int width = m;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) width = max(width, __shfl_xor_sync(0xffffffffu, width, o));
+    width = min((width + 3) & ~3, P.K & ~3);
+    for (int k = m; k < width; k++) {
+        P.ell_col[SELL(k, s)] = s;
+        P.ell_val[SELL(k, s)] = 0.0;
+    }
+    if ((threadIdx.x & 31) == 0) P.ell_width[s >> 5] = width;
     P.ell_count[s] = m;
     P.diag[s]      = diag;
 }
@@ -125,11 +135,10 @@ __global__ void __launch_bounds__(256) dirichlet_union_kernel(Params P) {
     int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= *P.n_active) return;
     const double re = P.s.re_pressure;
-    const size_t N  = (size_t) P.N;
     int cnt = P.nbr_count[s];
     for (int k = 0; k < cnt; k++) {
-        int j = P.nbr_idx[k * N + s];
-        if (j > s || !(P.nbr_dist[k * N + s] < re)) continue; // each undirected edge once
+        int j = P.nbr_idx[SELL(k, s)];
+        if (j > s || !(P.nbr_dist[SELL(k, s)] < re)) continue; // each undirected edge once
         int a = uf_find(P.parent, s), b = uf_find(P.parent, j);
         while (a != b) {
             if (a < b) { int t = a; a = b; b = t; }
@@ -168,13 +177,12 @@ __global__ void __launch_bounds__(256) min_pressure_kernel(Params P) {
     int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= *P.n_active || P.S.bc[s] == MPSB_BC_IGNORED) return;
     const double re = P.s.re_pressure;
-    const size_t N  = (size_t) P.N;
     double m = P.S.p[s];
     int cnt  = P.nbr_count[s];
     for (int k = 0; k < cnt; k++) {
-        double d = P.nbr_dist[k * N + s];
+        double d = P.nbr_dist[SELL(k, s)];
         if (d < re) {
-            int j = P.nbr_idx[k * N + s];
+            int j = P.nbr_idx[SELL(k, s)];
             if (P.S.type[j] == MPSB_DUMMY_WALL) continue;
             double pj = P.S.p[j];
             if (m > pj) m = pj;
@@ -196,7 +204,7 @@ void mpsb_launch_flags_source(mpsb_handle* h) {
 void mpsb_launch_matrix(mpsb_handle* h) {
     Params& P = h->P;
     cudaMemsetAsync(&P.stats->nnz, 0, sizeof(int), h->stream);
-    MPSB_LAUNCH(h, matrix_kernel, mpsb_div_up(P.N, 256), 256, 0, P);
+    MPSB_LAUNCH(h, matrix_kernel, mpsb_div_up(P.Np, 256) , 256, 0, P);
 }
 
 void mpsb_launch_dirichlet(mpsb_handle* h) {

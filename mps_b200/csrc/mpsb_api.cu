@@ -133,10 +133,12 @@ int mpsb_create(const mpsb_settings* settings, int64_t n, const int32_t* type, c
     Params& P = h->P;
     P.s = *settings;
     P.N = (int) n;
+    P.Np = (int) ((n + 31) / 32 * 32);
     derive(P);
     const char* envk = getenv("MPSB_MAX_NEIGHBORS");
     P.K = envk ? atoi(envk) : (settings->dim == 2 ? 64 : 384);
-    if (P.K < 1 || P.numCells <= 0) {
+    P.K = (P.K + 3) & ~3; // slices are padded in groups of 4 slots
+    if (P.K < 4 || P.numCells <= 0) {
         snprintf(g_create_error, sizeof g_create_error, "mpsb_create: bad neighbour capacity or cell grid");
         delete h;
         return MPSB_ERR_ARG;
@@ -168,7 +170,7 @@ int mpsb_create(const mpsb_settings* settings, int64_t n, const int32_t* type, c
     CKC(cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
     h->stream = h->own_stream;
     for (auto& ev : h->ev) CKC(cudaEventCreate(&ev));
-    size_t N = (size_t) P.N, KN = (size_t) P.K * N;
+    size_t N = (size_t) P.Np, KN = (size_t) P.K * N; // row arrays padded to whole slices
     Sorted& S = P.S;
     double** sd[] = {&S.x, &S.y, &S.z, &S.u, &S.v, &S.w, &S.u2, &S.v2, &S.w2, &S.ax, &S.ay, &S.az, &S.p, &S.minp, &S.ratio};
     for (double** p : sd) CKC(dalloc(p, N));
@@ -180,7 +182,7 @@ int mpsb_create(const mpsb_settings* settings, int64_t n, const int32_t* type, c
     CKC(dalloc(&P.key, N)); CKC(dalloc(&P.key_alt, N)); CKC(dalloc(&P.val, N)); CKC(dalloc(&P.val_alt, N));
     CKC(dalloc(&P.cell_start, (size_t) P.numCells)); CKC(dalloc(&P.cell_end, (size_t) P.numCells));
     CKC(dalloc(&P.nbr_count, N)); CKC(dalloc(&P.nbr_idx, KN)); CKC(dalloc(&P.nbr_dist, KN));
-    CKC(dalloc(&P.ell_count, N)); CKC(dalloc(&P.ell_col, KN)); CKC(dalloc(&P.ell_val, KN));
+    CKC(dalloc(&P.ell_count, N)); CKC(dalloc(&P.ell_width, N / 32 + 1)); CKC(dalloc(&P.ell_col, KN)); CKC(dalloc(&P.ell_val, KN));
     CKC(dalloc(&P.diag, N)); CKC(dalloc(&P.rhs, N));
     CKC(dalloc(&P.cg_r, N)); CKC(dalloc(&P.cg_p, N)); CKC(dalloc(&P.cg_ap, N)); CKC(dalloc(&P.cg_invdiag, N));
     CKC(dalloc(&P.parent, N)); CKC(dalloc(&P.mark, N));
@@ -199,12 +201,13 @@ int mpsb_create(const mpsb_settings* settings, int64_t n, const int32_t* type, c
         mpsb_destroy(h);
         return MPSB_ERR_CUDA;
     }
-    CKC(dalloc(&P.cg_partials, 3 * (size_t) h->cg_max_blocks));
+    CKC(dalloc(&P.cg_partials, 8 * (size_t) h->cg_max_blocks + 8));
+    CKC(dalloc(&P.cg_slice_pap, N / 32 + 1));
     // initial state: type/position/velocity from the caller, everything else 0 / Ignored (SURVEY B-1)
-    CKC(cudaMemcpy(H.type, type, sizeof(int) * N, cudaMemcpyHostToDevice));
-    CKC(cudaMemcpy(H.pos, position, sizeof(double) * 3 * N, cudaMemcpyHostToDevice));
-    CKC(cudaMemcpy(H.vel, velocity, sizeof(double) * 3 * N, cudaMemcpyHostToDevice));
-    if (N > 0) build_lists(h);
+    CKC(cudaMemcpy(H.type, type, sizeof(int) * (size_t) n, cudaMemcpyHostToDevice));
+    CKC(cudaMemcpy(H.pos, position, sizeof(double) * 3 * (size_t) n, cudaMemcpyHostToDevice));
+    CKC(cudaMemcpy(H.vel, velocity, sizeof(double) * 3 * (size_t) n, cudaMemcpyHostToDevice));
+    if (n > 0) build_lists(h);
     CKC(cudaStreamSynchronize(h->stream));
     CKC(cudaGetLastError());
 #undef CKC
@@ -222,7 +225,7 @@ int mpsb_destroy(mpsb_handle* h) {
     void* ptrs[] = {S.x, S.y, S.z, S.u, S.v, S.w, S.u2, S.v2, S.w2, S.ax, S.ay, S.az, S.p, S.minp, S.ratio, S.type,
                     S.bc, S.id, H.pos, H.vel, H.acc, H.p, H.minp, H.ratio, H.type, H.bc, H.inv, P.key, P.key_alt,
                     P.val, P.val_alt, P.cell_start, P.cell_end, P.nbr_count, P.nbr_idx, P.nbr_dist, P.ell_count,
-                    P.ell_col, P.ell_val, P.diag, P.rhs, P.cg_r, P.cg_p, P.cg_ap, P.cg_invdiag, P.cg_partials,
+                    P.ell_width, P.ell_col, P.ell_val, P.diag, P.rhs, P.cg_r, P.cg_p, P.cg_ap, P.cg_invdiag, P.cg_partials, P.cg_slice_pap,
                     P.parent, P.mark, P.cand, P.cand_count, P.ev_ghost_id, P.ev_ghost_xyz, P.ev_uncon_id, P.stats,
                     h->block_hist};
     for (void* p : ptrs)
@@ -418,8 +421,8 @@ int mpsb_get_neighbors(mpsb_handle* h, int64_t* row_start, int32_t* ids, double*
     *total       = k;
     if (!ids || !dist) return MPSB_OK;
     if (capacity < k) return MPSB_ERR_CAPACITY;
-    std::vector<int> idx((size_t) kmax * N);
-    std::vector<double> dd((size_t) kmax * N);
+    std::vector<int> idx((size_t) P.K * P.Np);
+    std::vector<double> dd((size_t) P.K * P.Np);
     if (kmax > 0) {
         CK(h, cudaMemcpy(idx.data(), P.nbr_idx, sizeof(int) * idx.size(), cudaMemcpyDeviceToHost));
         CK(h, cudaMemcpy(dd.data(), P.nbr_dist, sizeof(double) * dd.size(), cudaMemcpyDeviceToHost));
@@ -428,8 +431,8 @@ int mpsb_get_neighbors(mpsb_handle* h, int64_t* row_start, int32_t* ids, double*
         if (type[i] == MPSB_GHOST) continue;
         size_t s = (size_t) inv[i];
         for (int m = 0; m < cnt[s]; m++) {
-            ids[row_start[i] + m]  = sid[idx[(size_t) m * N + s]];
-            dist[row_start[i] + m] = dd[(size_t) m * N + s];
+            ids[row_start[i] + m]  = sid[idx[mpsb_sell(m, (int) s, P.K)]];
+            dist[row_start[i] + m] = dd[mpsb_sell(m, (int) s, P.K)];
         }
     }
     return MPSB_OK;
@@ -464,8 +467,8 @@ int mpsb_get_ppe(mpsb_handle* h, int64_t* row_start, int32_t* col, double* val, 
     *nnz         = k;
     if (!col || !val) return MPSB_OK;
     if (capacity < k) return MPSB_ERR_CAPACITY;
-    std::vector<int> ec((size_t) kmax * N);
-    std::vector<double> ev((size_t) kmax * N);
+    std::vector<int> ec((size_t) P.K * P.Np);
+    std::vector<double> ev((size_t) P.K * P.Np);
     if (kmax > 0) {
         CK(h, cudaMemcpy(ec.data(), P.ell_col, sizeof(int) * ec.size(), cudaMemcpyDeviceToHost));
         CK(h, cudaMemcpy(ev.data(), P.ell_val, sizeof(double) * ev.size(), cudaMemcpyDeviceToHost));
@@ -475,7 +478,7 @@ int mpsb_get_ppe(mpsb_handle* h, int64_t* row_start, int32_t* col, double* val, 
         size_t s = (size_t) inv[i];
         if (bc[s] != MPSB_BC_INNER) continue;
         row.clear();
-        for (int m = 0; m < cnt[s]; m++) row.push_back({sid[ec[(size_t) m * N + s]], ev[(size_t) m * N + s]});
+        for (int m = 0; m < cnt[s]; m++) row.push_back({sid[ec[mpsb_sell(m, (int) s, P.K)]], ev[mpsb_sell(m, (int) s, P.K)]});
         row.push_back({(int) i, diag[s]});
         std::sort(row.begin(), row.end(), [](const auto& a, const auto& c) { return a.first < c.first; });
         for (size_t m = 0; m < row.size(); m++) {
@@ -483,6 +486,21 @@ int mpsb_get_ppe(mpsb_handle* h, int64_t* row_start, int32_t* col, double* val, 
             val[row_start[i] + (int64_t) m] = row[m].second;
         }
     }
+    return MPSB_OK;
+}
+
+int mpsb_debug_cg_cycles(const mpsb_handle* h, int64_t* out4) {
+    if (!h || !out4) return MPSB_ERR_ARG;
+    for (int k = 0; k < 4; k++) out4[k] = h->host_stats.cg_cycles[k];
+    return MPSB_OK;
+}
+
+int mpsb_debug_cg_block_cycles(mpsb_handle* h, int64_t* out, int capacity_blocks, int* nblocks) {
+    if (!h || !out || !nblocks) return MPSB_ERR_ARG;
+    int mb = h->cg_max_blocks;
+    *nblocks = mb;
+    if (capacity_blocks < mb) return MPSB_ERR_CAPACITY;
+    CK(h, cudaMemcpy(out, h->P.cg_partials + 3 * (size_t) mb, sizeof(int64_t) * 5 * (size_t) mb, cudaMemcpyDeviceToHost));
     return MPSB_OK;
 }
 

@@ -5,8 +5,10 @@
 //   * HOME  (id order, packed xyz)  — what upload/download move; authoritative between API calls.
 //   * SORTED (cell-major, then id; SoA) — the working set of every kernel of the step. Built by
 //     the cell-list build (key -> radix sort -> gather); all neighbour indices are SORTED indices.
-// Neighbour lists and the PPE matrix are slot-major ELL: entry k of row s lives at [k * N + s],
-// so a warp that owns 32 consecutive rows reads 32 consecutive values per slot (coalesced).
+// Neighbour lists and the PPE matrix are SLICED ELL (slice = the 32 rows of one warp, fixed slice
+// pitch K slots): entry k of row s lives at [((s / 32) * K + k) * 32 + s % 32]. A warp reads 32
+// consecutive values per slot (coalesced) AND the slots of a slice are contiguous, so a whole slice
+// of the matrix is one contiguous block that the PCG kernel streams with 1-D TMA bulk copies.
 #pragma once
 #include "../../include/mps_b200.h"
 
@@ -31,6 +33,7 @@ struct DevStats {
     int max_neighbors;
     int error_flags; // bit0 capacity, bit1 out-of-grid, bit2 event overflow
     int pad[2];
+    long long cg_cycles[4]; // CTA 0's SM cycles in sweep A / B / C / reductions+grid barriers (diagnostic)
 };
 
 // Sorted-order SoA working set (all arrays have N entries).
@@ -56,7 +59,8 @@ struct Home {
 struct Params {
     mpsb_settings s;
     int N;        // particle slots (ghosts included)
-    int K;        // neighbour-list capacity per particle
+    int Np;       // N rounded up to a whole number of 32-row slices (allocation size of row arrays)
+    int K;        // neighbour-list capacity per particle (slice pitch in slots)
     int numX, numY, numZ, numCells;
     // derived coefficients, computed on the host with the reference's operation order
     double visc_coef;    // nu * (2*dim) / (n0_v * lambda_v)          src/mps.cpp:182
@@ -80,12 +84,14 @@ struct Params {
     int *nbr_idx;              // K*N
     double *nbr_dist;          // K*N
     // PPE: ELL off-diagonals + diagonal + rhs; CG vectors
-    int *ell_count;            // N
-    int *ell_col;              // K*N
-    double *ell_val;           // K*N
+    int *ell_count;            // Np  true off-diagonal count of the row
+    int *ell_width;            // Np/32  padded slot count of the slice (multiple of 4; padding = (col row, val 0))
+    int *ell_col;              // K*Np
+    double *ell_val;           // K*Np
     double *diag, *rhs;        // N
     double *cg_r, *cg_p, *cg_ap, *cg_invdiag; // N
-    double *cg_partials;       // 3 * max_blocks
+    double *cg_partials;       // 8 * max_blocks + 1: 3 reduction rows, 5 diagnostic rows, 2 slice-queue counters
+    double *cg_slice_pap;      // Np/32 + 1: p.Ap of each 32-row slice (deterministic two-level sum)
     // Dirichlet connectivity
     int *parent;               // N
     int *mark;                 // N
@@ -108,6 +114,8 @@ struct mpsb_handle {
     int sort_bits;
     int cg_max_blocks;      // cooperative grid limit for the PCG kernel
     int cg_threads;
+    int cg_smem;            // dynamic shared memory of the PCG kernel
+    int cg_iteration_cap;   // diagnostic: stop the solve after this many iterations (0 = Eigen's 2N)
     int num_sms;
     int64_t launches;
     bool have_lists;        // a neighbour build has happened since the last position upload
@@ -144,6 +152,12 @@ int mpsb_pcg_configure(mpsb_handle* h);
     } while (0)
 
 static inline int mpsb_div_up(int a, int b) { return (a + b - 1) / b; }
+
+// sliced-ELL index of slot k of row s for slice pitch K
+__host__ __device__ __forceinline__ size_t mpsb_sell(int k, int s, int K) {
+    return ((size_t) (s >> 5) * (size_t) K + (size_t) k) * 32u + (size_t) (s & 31);
+}
+#define SELL(k, s) mpsb_sell((k), (s), P.K)
 
 #ifdef __CUDACC__
 // weight (reference src/mps.cpp:9-16); every operation individually rounded (no FMA: the
