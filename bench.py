@@ -246,7 +246,9 @@ def run_gpu_arm(args):
         peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
     solve_bytes = sum(s["cg_iterations"] * (12.0 * s["nnz"] + 108.0 * s["n_inner"]) + 32.0 * s["n_inner"] for s in stats)
     solve_ms = sum(s["ms_solve"] for s in stats)
-    achieved = solve_bytes / (solve_ms * 1e-3) / 1e9 if solve_ms > 0 else 0.0
+    # N > 1: each rank streams its own row block, so the per-GPU figure (1/world of the bytes) is the one
+    # that compares with one GPU's HBM peak
+    achieved = solve_bytes / world / (solve_ms * 1e-3) / 1e9 if solve_ms > 0 else 0.0
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "pcg_traffic.json")
     if os.path.exists(tpath):
@@ -255,7 +257,7 @@ def run_gpu_arm(args):
             traffic = tj.get("dram_bytes_per_launch")
     roofline = {"kernel": "pcg_kernel (persistent Jacobi-PCG, 1 launch per step)", "bound": "hbm",
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                "peak_source": peak_src, "bytes_per_launch": solve_bytes / len(stats),
+                "peak_source": peak_src, "per_gpu": True, "bytes_per_launch": solve_bytes / world / len(stats),
                 "ms_per_launch": solve_ms / len(stats)}
     mean = lambda k: sum(s[k] for s in stats) / len(stats)  # noqa: E731
 

@@ -18,6 +18,7 @@ NVCC_FLAGS = [
     "-O3", "-lineinfo", "-std=c++17",
     "-fmad=false",            # parity: every fp64 op individually rounded
     "-Xcompiler", "-fPIC", "-shared",
+    "-ldl",                   # NCCL is bound with dlopen (mpsb_comm.cu)
 ]
 
 

@@ -112,6 +112,44 @@ def load_library():
     return lib
 
 
+def new_unique_id(lib=None):
+    """128-byte ncclUniqueId from mpsb_comm_unique_id (rank 0 only)."""
+    lib = lib or load_library()
+    buf = (ct.c_char * 128)()
+    rc = lib.mpsb_comm_unique_id(buf)
+    if rc != 0:
+        raise MpsError(rc, "mpsb_comm_unique_id failed (libnccl.so.2 not loadable?)")
+    return bytes(buf.raw)
+
+
+def distribute_unique_id(rank, make_id, group=None):
+    """The id made by `make_id()` on rank 0, on every rank of the torch.distributed group."""
+    import torch
+    import torch.distributed as dist
+
+    box = [make_id() if rank == 0 else None]
+    dist.broadcast_object_list(box, src=0, group=group, device=torch.device("cpu") if dist.get_backend(group) == "gloo" else None)
+    uid = box[0]
+    if not isinstance(uid, (bytes, bytearray)) or len(uid) != 128:
+        raise ValueError("unique id must be 128 bytes")
+    return bytes(uid)
+
+
+def row_block(np_rows, rank, world):
+    """Rows [lo, hi) of the padded sorted order that `rank` solves (k_pcg.cu: rows_per_rank = Np / world);
+    np_rows = N rounded up to a multiple of 256 (mpsb_api.cu), so 1/2/4/8 ranks get whole 32-row slices."""
+    if world not in (1, 2, 4, 8) or not 0 <= rank < world:
+        raise ValueError("supported world sizes: 1, 2, 4, 8")
+    if np_rows % 256:
+        raise ValueError("np_rows must be a multiple of 256")
+    per = np_rows // world
+    return rank * per, (rank + 1) * per
+
+
+def padded_rows(n):
+    return (int(n) + 255) // 256 * 256
+
+
 class DeviceMPS:
     """One MPS simulation state resident on one B200."""
 
@@ -231,6 +269,18 @@ class DeviceMPS:
         self._check(self.lib.mpsb_events(self.h, kind, ids.ctypes.data, xyz.ctypes.data, capacity, ct.byref(cnt)))
         m = min(cnt.value, capacity)
         return ids[:m], xyz[:m]
+
+    # --- multi-GPU (one process per GPU) ---------------------------------------------------------
+    def attach_comm(self, rank, world, unique_id128):
+        """Join the `world`-rank exchange group (include/mps_b200.h: mpsb_attach_comm)."""
+        buf = (ct.c_char * 128).from_buffer_copy(bytes(unique_id128))
+        self._check(self.lib.mpsb_attach_comm(self.h, int(rank), int(world), buf))
+        self.rank, self.world = int(rank), int(world)
+
+    def attach_comm_torch(self, rank, world, group=None):
+        """Rank 0 makes the NCCL unique id, torch.distributed (any backend) hands it to the others."""
+        uid = distribute_unique_id(rank, lambda: new_unique_id(self.lib), group)
+        self.attach_comm(rank, world, uid)
 
     def set_stream(self, cuda_stream_ptr):
         """Run on the caller's CUDA stream (e.g. torch.cuda.current_stream().cuda_stream)."""

@@ -19,6 +19,14 @@
 //   sweep B  x += a p; r -= a ap; |r|^2, r.z   read x,p,r,ap,invdiag, write x,r = 56n   (16-byte vectors)
 //   sweep C  p = z + b p (z = invdiag r)       read r,invdiag,p, write p = 32n
 // = 12 nnz + 108 n algorithmic bytes, the figure bench.py's roofline uses.
+//
+// Multi-GPU (template MULTI): rank g solves the rows of its y-slab (a contiguous block of
+// slices) in the SAME persistent kernel; nothing returns to the host between iterations and no NCCL call
+// sits on the Krylov path. The three per-iteration global steps are fused device-side exchanges over
+// NVLink peer memory: (1) p.ap, (2) |r|^2 and r.z — each rank's partial is stored into every peer's inbox
+// and every rank adds the partials in rank order, so all ranks hold bit-identical scalars and take the
+// same branches; (3) the halo rows of the new p, which sweep C stores directly into the neighbouring
+// ranks' p vectors, published by the same flag exchange that acts as the cross-GPU barrier.
 #include "mpsb_internal.cuh"
 
 #include <cfloat>
@@ -54,6 +62,8 @@ struct Smem {
     StageMeta meta[PCG_WARPS][PCG_STAGES];
     unsigned long long full[PCG_WARPS][PCG_STAGES];
     double red[66];
+    int need[MPSB_MAX_RANKS][2]; // MULTI: my rows each peer reads, [lo, hi)
+    int flag;                    // MULTI: this CTA arrived last at the running exchange
 };
 
 __device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned) __cvta_generic_to_shared(p); }
@@ -88,14 +98,24 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned by
                  : "memory");
 }
 
-// Deterministic block-wide sum of two values; result broadcast to every thread.
+// Deterministic block-wide reduction of two values; result broadcast to every thread.
+// MINMAX: a is reduced with min, b with max (halo extents); otherwise both are summed.
+template <bool MINMAX>
+__device__ __forceinline__ void combine2(double& a, double& b, double oa, double ob) {
+    if (MINMAX) {
+        a = fmin(a, oa);
+        b = fmax(b, ob);
+    } else {
+        a += oa;
+        b += ob;
+    }
+}
+template <bool MINMAX = false>
 __device__ __forceinline__ void block_sum2(double& a, double& b, double* sh /* 66 */) {
     int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        a += __shfl_xor_sync(0xffffffffu, a, o);
-        b += __shfl_xor_sync(0xffffffffu, b, o);
-    }
+    for (int o = 16; o > 0; o >>= 1)
+        combine2<MINMAX>(a, b, __shfl_xor_sync(0xffffffffu, a, o), __shfl_xor_sync(0xffffffffu, b, o));
     __syncthreads(); // protect sh from the previous use
     if (lane == 0) {
         sh[warp]      = a;
@@ -103,12 +123,11 @@ __device__ __forceinline__ void block_sum2(double& a, double& b, double* sh /* 6
     }
     __syncthreads();
     if (warp == 0) {
-        double va = lane < PCG_WARPS ? sh[lane] : 0.0, vb = lane < PCG_WARPS ? sh[32 + lane] : 0.0;
+        double va = sh[lane < PCG_WARPS ? lane : 0], vb = sh[32 + (lane < PCG_WARPS ? lane : 0)];
+        if (!MINMAX && lane >= PCG_WARPS) va = vb = 0.0;
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            va += __shfl_xor_sync(0xffffffffu, va, o);
-            vb += __shfl_xor_sync(0xffffffffu, vb, o);
-        }
+        for (int o = 16; o > 0; o >>= 1)
+            combine2<MINMAX>(va, vb, __shfl_xor_sync(0xffffffffu, va, o), __shfl_xor_sync(0xffffffffu, vb, o));
         if (lane == 0) {
             sh[64] = va;
             sh[65] = vb;
@@ -132,6 +151,88 @@ __device__ __forceinline__ void grid_sum2(const double* pa, const double* pb, in
     b = lb;
 }
 
+// ---- cross-GPU exchange (MULTI) ------------------------------------------------------------------
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+struct Xchg {
+    unsigned long long epoch; // exchanges completed by this rank since attach (same on every rank)
+    unsigned long long count; // exchanges completed in this launch
+};
+
+// One fused all-to-all + barrier over all CTAs of all ranks. Every CTA contributes (a, b); on return every
+// thread of every rank can read each rank's combined pair from its inbox (xchg_slot). Steps:
+//   1. CTA partials -> local array; fence.sys (publishes this CTA's earlier remote p stores too: the
+//      fence of thread 0 after the CTA barrier is cumulative); arrive on the local counter.
+//   2. The CTA that arrives last combines the partials in index order (deterministic, whoever is last) and
+//      stores the rank's pair into the inbox of every rank, then the epoch flag with release.sys.
+//   3. Every CTA waits until all W flags in its OWN inbox (local HBM, no NVLink polling) reach the epoch.
+// It subsumes a grid-wide barrier. A rank that never arrives (crashed peer) trips the timeout -> trap,
+// which fails the launch loudly instead of hanging the box.
+template <bool MINMAX>
+__device__ __forceinline__ void xchg_all(const Params& P, Xchg& xs, double a, double b, double* part0, double* part1,
+                                         double* sh, int* sflag) {
+    const PeerLinks& L = P.L;
+    const int W = L.world, nblocks = gridDim.x;
+    xs.epoch++;
+    xs.count++;
+    block_sum2<MINMAX>(a, b, sh);
+    if (threadIdx.x == 0) {
+        part0[blockIdx.x] = a;
+        part1[blockIdx.x] = b;
+        __threadfence_system();
+        unsigned long long t = atomicAdd(L.arrive, 1ull);
+        *sflag = (t + 1ull == xs.count * (unsigned long long) nblocks) ? 1 : 0;
+    }
+    __syncthreads();
+    if (*sflag) {
+        __threadfence_system();
+        double la = MINMAX ? DBL_MAX : 0.0, lb = MINMAX ? -DBL_MAX : 0.0;
+        for (int i = threadIdx.x; i < nblocks; i += PCG_THREADS) combine2<MINMAX>(la, lb, __ldcg(part0 + i), __ldcg(part1 + i));
+        block_sum2<MINMAX>(la, lb, sh);
+        if ((int) threadIdx.x < W) {
+            const int q = threadIdx.x;
+            double* dst = L.peer_red[q] + ((size_t) (xs.epoch & 1ull) * MPSB_MAX_RANKS + L.rank) * 4;
+            asm volatile("st.relaxed.sys.global.v2.f64 [%0], {%1, %2};" ::"l"(dst), "d"(la), "d"(lb) : "memory");
+            st_release_sys(L.peer_flag[q] + L.rank, xs.epoch);
+        }
+    }
+    if ((int) threadIdx.x < W) {
+        const unsigned long long t0 = global_timer_ns();
+        while (ld_acquire_sys(L.flag + threadIdx.x) < xs.epoch) {
+            if (global_timer_ns() - t0 > 20000000000ull) { // 20 s: a peer is gone
+                atomicOr(&P.stats->error_flags, 8);
+                __threadfence_system();
+                __trap();
+            }
+        }
+    }
+    __syncthreads();
+}
+__device__ __forceinline__ double xchg_slot(const Params& P, const Xchg& xs, int q, int k) {
+    return __ldcg(P.L.red + ((size_t) (xs.epoch & 1ull) * MPSB_MAX_RANKS + q) * 4 + k);
+}
+// sum over ranks in rank order: bit-identical on every rank
+__device__ __forceinline__ void xchg_sum2(const Params& P, const Xchg& xs, double& a, double& b) {
+    a = 0.0;
+    b = 0.0;
+    for (int q = 0; q < P.L.world; q++) {
+        a += xchg_slot(P, xs, q, 0);
+        b += xchg_slot(P, xs, q, 1);
+    }
+}
+
 // Ring bookkeeping of one warp; serial numbers keep running across sweeps so the mbarrier phase
 // parity of stage (serial % STAGES) is (serial / STAGES) & 1.
 struct Pipe {
@@ -147,14 +248,14 @@ constexpr int PCG_BATCH = 2; // slices taken from the global queue per atomic
 // cost 25 % of the sweep. Determinism is kept by storing p.ap PER SLICE (warp-reduced in a fixed order)
 // into slice_pap[]; the caller sums that array in a fixed order. Rows of a slice beyond n carry diag 0 /
 // padding only and p = 0 there.
-__device__ __forceinline__ void spmv_sweep(const Params& P, Smem& sm, Pipe& pipe, int n, const double* p, double* ap,
-                                           unsigned* ticket, double* slice_pap) {
+// The sweep covers slices [sbeg, nslices) (a rank's row block; sbeg = 0 on one GPU).
+__device__ __forceinline__ void spmv_sweep(const Params& P, Smem& sm, Pipe& pipe, int sbeg, int nslices, const double* p,
+                                           double* ap, unsigned* ticket, double* slice_pap) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int nslices = (n + 31) >> 5;
-    const size_t K    = (size_t) P.K;
+    const size_t K = (size_t) P.K;
     auto take = [&]() -> int { // lane 0 holds the result; shuffled when needed
         int v = 0;
-        if (lane == 0) v = (int) atomicAdd(ticket, (unsigned) PCG_BATCH);
+        if (lane == 0) v = sbeg + (int) atomicAdd(ticket, (unsigned) PCG_BATCH);
         return v;
     };
     auto widths = [&](int s0) -> int { return (lane < PCG_BATCH && s0 + lane < nslices) ? P.ell_width[s0 + lane] : 0; };
@@ -237,6 +338,8 @@ __device__ __forceinline__ void spmv_sweep(const Params& P, Smem& sm, Pipe& pipe
     }
 }
 
+// MULTI = false: one GPU, rows [0, n). MULTI = true: this rank's row block; see the file header.
+template <bool MULTI>
 __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_blocks, int iteration_cap) {
     cg::grid_group grid = cg::this_grid();
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -256,6 +359,15 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
     double* part2 = part1 + max_blocks;
     unsigned* tickets = reinterpret_cast<unsigned*>(P.cg_partials + 8 * (size_t) max_blocks); // 2 slice queues
 
+    // this rank's rows: [row_lo, row_hi) of the padded Np rows, of which [row_lo, act_hi) are active (< n)
+    const int W = MULTI ? P.L.world : 1, rank = MULTI ? P.L.rank : 0;
+    const int rows_per_rank = P.Np / W;               // Np is a multiple of 32 * 8
+    const int row_lo = rank * rows_per_rank, row_hi = row_lo + rows_per_rank;
+    const int act_hi = max(row_lo, min(row_hi, n));
+    const int sl_lo = row_lo >> 5, sl_hi = (act_hi + 31) >> 5; // slices with at least one active row
+    Xchg xs{0ull, 0ull};
+    if (MULTI) xs.epoch = *P.L.epoch;
+
     if (threadIdx.x < PCG_WARPS * PCG_STAGES) mbar_init(&sm.full[0][0] + threadIdx.x, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     __syncthreads();
@@ -263,7 +375,7 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
 
     // setup: x = 0, r = b, invdiag, p = invdiag r (0 beyond n, up to the slice padding); |b|^2 and r.p
     double l0 = 0.0, l1 = 0.0;
-    for (int i = tid; i < P.Np; i += stride) {
+    for (int i = row_lo + tid; i < row_hi; i += stride) {
         if (i < P.N) x[i] = 0.0;
         double pi = 0.0;
         if (i < n) {
@@ -276,14 +388,55 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
         }
         p[i] = pi;
     }
-    block_sum2(l0, l1, sh);
-    if (threadIdx.x == 0) {
-        part0[blockIdx.x] = l0;
-        part1[blockIdx.x] = l1;
+    // MULTI: which of my rows each peer reads in its sweep A. Every rank publishes the column extent of
+    // its row block [need_lo, need_hi]; the rows of mine inside a peer's extent are pushed to that peer
+    // whenever p changes (here and in sweep C). push_gap_* bracket the rows nobody else needs.
+    int push_gap_lo = row_lo, push_gap_hi = row_hi;
+    if (MULTI) {
+        double cmn = DBL_MAX, cmx = -DBL_MAX;
+        for (int sl = sl_lo + tid; sl < sl_hi; sl += stride) {
+            cmn = fmin(cmn, (double) P.ell_cmin[sl]);
+            cmx = fmax(cmx, (double) P.ell_cmax[sl]);
+        }
+        xchg_all<true>(P, xs, cmn, cmx, part0, part1, sh, &sm.flag);
+        if ((int) threadIdx.x < W) {
+            const int q = threadIdx.x;
+            double a = xchg_slot(P, xs, q, 0), b = xchg_slot(P, xs, q, 1);
+            int lo = 0, hi = 0; // empty: a rank without active rows needs nothing
+            if (a <= b && q != rank) {
+                lo = max((int) a, row_lo);
+                hi = min((int) b + 1, row_hi);
+                if (hi < lo) hi = lo;
+            }
+            sm.need[q][0] = lo;
+            sm.need[q][1] = hi;
+        }
+        __syncthreads();
+        for (int q = 0; q < W; q++) {
+            if (sm.need[q][1] <= sm.need[q][0]) continue;
+            if (q < rank) push_gap_lo = max(push_gap_lo, sm.need[q][1]);
+            else push_gap_hi = min(push_gap_hi, sm.need[q][0]);
+        }
+        // first halo push: rows of the initial p that peers read (written above by other threads; the
+        // exchange just passed is a barrier over this rank's CTAs)
+        for (int q = 0; q < W; q++) {
+            double* dst = P.L.peer_p[q];
+            for (int i = sm.need[q][0] + tid; i < sm.need[q][1]; i += stride) dst[i] = p[i];
+        }
     }
-    grid.sync();
     double rhsNorm2, absNew;
-    grid_sum2(part0, part1, nblocks, rhsNorm2, absNew, sh);
+    if (MULTI) {
+        xchg_all<false>(P, xs, l0, l1, part0, part1, sh, &sm.flag);
+        xchg_sum2(P, xs, rhsNorm2, absNew);
+    } else {
+        block_sum2(l0, l1, sh);
+        if (threadIdx.x == 0) {
+            part0[blockIdx.x] = l0;
+            part1[blockIdx.x] = l1;
+        }
+        grid.sync();
+        grid_sum2(part0, part1, nblocks, rhsNorm2, absNew, sh);
+    }
     int it = 0;
     double residualNorm2 = rhsNorm2;
     bool done = false;
@@ -293,18 +446,25 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
     }
     const double threshold = fmax(DBL_EPSILON * DBL_EPSILON * rhsNorm2, DBL_MIN);
     if (!done && residualNorm2 < threshold) done = true;
-    grid.sync(); // part0/part1 are reused below
+    if (!MULTI) grid.sync(); // part0/part1 are reused below
     const int maxIters = iteration_cap > 0 ? iteration_cap : 2 * P.N;
-    const int npairs = n >> 1;
+    // sweeps B and C walk the active rows of the block two at a time (row_lo is even)
+    const int pair_lo = row_lo >> 1, pair_hi = pair_lo + ((act_hi - row_lo) >> 1);
+    const bool odd_tail = ((act_hi - row_lo) & 1) != 0; // row act_hi - 1 is left over
+
+    // MULTI: store row i of the new p into the p vector of every peer that reads it
+    auto push_row = [&](int i, double v) {
+        if (i >= push_gap_lo && i < push_gap_hi) return;
+        for (int q = 0; q < W; q++)
+            if (i >= sm.need[q][0] && i < sm.need[q][1]) P.L.peer_p[q][i] = v;
+    };
 
     long long cyc[4] = {0, 0, 0, 0}, t0 = clock64(), t1;
 #define PCG_TICK(slot) do { t1 = clock64(); cyc[slot] += t1 - t0; t0 = t1; } while (0)
     while (!done && it < maxIters) {
         // ---- sweep A: ap = A p, p.ap ----
         unsigned* ticket = tickets + (it & 1);
-#if !(PCG_EXP == 11 || PCG_EXP == 12)
-        spmv_sweep(P, sm, pipe, n, p, ap, ticket, P.cg_slice_pap);
-#endif
+        spmv_sweep(P, sm, pipe, sl_lo, sl_hi, p, ap, ticket, P.cg_slice_pap);
         __syncthreads();
         PCG_TICK(0);
         grid.sync();
@@ -312,21 +472,26 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
         if (tid == 0) tickets[(it + 1) & 1] = 0u; // the other counter is idle until the next sweep A
         double lpap = 0.0, dummy = 0.0;
         {
-            const int nslices = (n + 31) >> 5, per = (nslices + nblocks - 1) / nblocks;
-            const int lo = blockIdx.x * per, hi = min(lo + per, nslices);
+            const int nsl = sl_hi - sl_lo, per = (nsl + nblocks - 1) / nblocks;
+            const int lo = sl_lo + blockIdx.x * per, hi = min(lo + per, sl_hi);
             for (int i = lo + (int) threadIdx.x; i < hi; i += PCG_THREADS) lpap += __ldcg(P.cg_slice_pap + i);
         }
-        block_sum2(lpap, dummy, sh);
-        if (threadIdx.x == 0) part0[blockIdx.x] = lpap;
-        grid.sync();
         double pap, unused;
-        grid_sum2(part0, part0, nblocks, pap, unused, sh);
+        if (MULTI) {
+            xchg_all<false>(P, xs, lpap, dummy, part0, part1, sh, &sm.flag);
+            xchg_sum2(P, xs, pap, unused);
+        } else {
+            block_sum2(lpap, dummy, sh);
+            if (threadIdx.x == 0) part0[blockIdx.x] = lpap;
+            grid.sync();
+            grid_sum2(part0, part0, nblocks, pap, unused, sh);
+        }
         const double alpha = absNew / pap;
         PCG_TICK(3);
         // ---- sweep B: x += alpha p; r -= alpha ap; |r|^2; r.z  (two rows per thread, 16-byte accesses) ----
         double lrr = 0.0, lrz = 0.0;
 #pragma unroll 2
-        for (int i = tid; i < (PCG_EXP == 10 || PCG_EXP == 12 ? 0 : npairs); i += stride) {
+        for (int i = pair_lo + tid; i < pair_hi; i += stride) {
             double2 pp = reinterpret_cast<const double2*>(p)[i], rr = reinterpret_cast<const double2*>(r)[i];
             double2 aa = reinterpret_cast<const double2*>(ap)[i], dd = reinterpret_cast<const double2*>(invd)[i];
             double2 xx = reinterpret_cast<const double2*>(x)[i];
@@ -337,8 +502,8 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
             lrr += rr.x * rr.x; lrr += rr.y * rr.y;
             lrz += rr.x * (dd.x * rr.x); lrz += rr.y * (dd.y * rr.y);
         }
-        if ((n & 1) && tid == 0) {
-            int i = n - 1;
+        if (odd_tail && tid == 0) {
+            int i = act_hi - 1;
             double ri = r[i] - alpha * ap[i];
             x[i] += alpha * p[i];
             r[i] = ri;
@@ -346,31 +511,46 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
             lrz += ri * (invd[i] * ri);
         }
         PCG_TICK(1);
-        block_sum2(lrr, lrz, sh);
-        if (threadIdx.x == 0) {
-            part1[blockIdx.x] = lrr;
-            part2[blockIdx.x] = lrz;
-        }
-        grid.sync();
         double rz;
-        grid_sum2(part1, part2, nblocks, residualNorm2, rz, sh);
-        if (PCG_EXP < 10 && residualNorm2 < threshold) break;
+        if (MULTI) {
+            xchg_all<false>(P, xs, lrr, lrz, part1, part2, sh, &sm.flag);
+            xchg_sum2(P, xs, residualNorm2, rz);
+        } else {
+            block_sum2(lrr, lrz, sh);
+            if (threadIdx.x == 0) {
+                part1[blockIdx.x] = lrr;
+                part2[blockIdx.x] = lrz;
+            }
+            grid.sync();
+            grid_sum2(part1, part2, nblocks, residualNorm2, rz, sh);
+        }
+        if (residualNorm2 < threshold) break;
         const double beta = rz / absNew;
         absNew = rz;
         PCG_TICK(3);
-        // ---- sweep C: p = z + beta p ----
+        // ---- sweep C: p = z + beta p (MULTI: halo rows also go to the peers that read them) ----
 #pragma unroll 2
-        for (int i = tid; i < (PCG_EXP == 10 || PCG_EXP == 12 ? 0 : npairs); i += stride) {
+        for (int i = pair_lo + tid; i < pair_hi; i += stride) {
             double2 pp = reinterpret_cast<const double2*>(p)[i], rr = reinterpret_cast<const double2*>(r)[i];
             double2 dd = reinterpret_cast<const double2*>(invd)[i];
             pp.x = dd.x * rr.x + beta * pp.x;
             pp.y = dd.y * rr.y + beta * pp.y;
             reinterpret_cast<double2*>(p)[i] = pp;
+            if (MULTI) {
+                push_row(2 * i, pp.x);
+                push_row(2 * i + 1, pp.y);
+            }
         }
-        if ((n & 1) && tid == 0) p[n - 1] = invd[n - 1] * r[n - 1] + beta * p[n - 1];
+        if (odd_tail && tid == 0) {
+            int i = act_hi - 1;
+            double v = invd[i] * r[i] + beta * p[i];
+            p[i] = v;
+            if (MULTI) push_row(i, v);
+        }
         it++;
         PCG_TICK(2);
-        grid.sync();
+        if (MULTI) xchg_all<false>(P, xs, 0.0, 0.0, part0, part1, sh, &sm.flag); // barrier + publishes the halo rows
+        else grid.sync();
         PCG_TICK(3);
     }
     if (threadIdx.x == 0) { // per-CTA diagnostic rows behind the three reduction rows
@@ -385,6 +565,7 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
         P.stats->cg_iterations   = it;
         P.stats->rhs_norm2       = rhsNorm2;
         P.stats->cg_rel_residual = rhsNorm2 > 0.0 ? sqrt(residualNorm2 / rhsNorm2) : 0.0;
+        if (MULTI) *P.L.epoch = xs.epoch; // every CTA read the old value before its first exchange
     }
 }
 
@@ -392,9 +573,10 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
 
 int mpsb_pcg_configure(mpsb_handle* h) {
     int smem = (int) sizeof(Smem);
-    if (cudaFuncSetAttribute(pcg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return -1;
+    if (cudaFuncSetAttribute(pcg_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return -1;
+    if (cudaFuncSetAttribute(pcg_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return -1;
     int per_sm = 0;
-    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, pcg_kernel, PCG_THREADS, smem);
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, pcg_kernel<true>, PCG_THREADS, smem);
     if (e != cudaSuccess || per_sm < 1) return -1;
     h->cg_threads    = PCG_THREADS;
     h->cg_smem       = smem;
@@ -406,15 +588,17 @@ int mpsb_pcg_configure(mpsb_handle* h) {
 
 void mpsb_launch_pcg(mpsb_handle* h) {
     Params& P = h->P;
+    const bool multi = P.L.world > 1;
     // one 32-row slice per warp at least; never more CTAs than can be co-resident (cooperative launch)
-    int want = mpsb_div_up(P.Np / 32, PCG_WARPS);
+    int want = mpsb_div_up(P.Np / 32 / (multi ? P.L.world : 1), PCG_WARPS);
     int grid = want < h->cg_max_blocks ? want : h->cg_max_blocks;
     if (grid < 1) grid = 1;
     int max_blocks = h->cg_max_blocks;
     cudaMemsetAsync(P.cg_partials + 8 * (size_t) max_blocks, 0, 8, h->stream); // the two slice-queue counters
+    if (multi) cudaMemsetAsync(P.L.arrive, 0, sizeof(unsigned long long), h->stream);
     int cap = h->cg_iteration_cap;
     void* args[] = {(void*) &P, (void*) &max_blocks, (void*) &cap};
-    cudaLaunchCooperativeKernel((const void*) pcg_kernel, dim3(grid), dim3(PCG_THREADS), args, (size_t) h->cg_smem,
-                                h->stream);
+    const void* fn = multi ? (const void*) pcg_kernel<true> : (const void*) pcg_kernel<false>;
+    cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(PCG_THREADS), args, (size_t) h->cg_smem, h->stream);
     h->launches++;
 }

@@ -72,7 +72,7 @@ __global__ void __launch_bounds__(256) source_ho_kernel(Params P) {
 __global__ void __launch_bounds__(256) matrix_kernel(Params P) {
     int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= P.Np) return; // Np is a multiple of 32: whole warps leave together
-    int m = 0;
+    int m = 0, cmin = s, cmax = s;
     double diag = 0.0;
     if (s < *P.n_active && P.S.bc[s] == MPSB_BC_INNER) {
         const double re = P.s.re_pressure;
@@ -88,6 +88,8 @@ __global__ void __launch_bounds__(256) matrix_kernel(Params P) {
                 if (bcj == MPSB_BC_INNER) {
                     P.ell_col[SELL(m, s)] = j;
                     P.ell_val[SELL(m, s)] = -a;
+                    cmin = min(cmin, j);
+                    cmax = max(cmax, j);
                     m++;
                 }
             }
@@ -97,13 +99,21 @@ __global__ void __launch_bounds__(256) matrix_kernel(Params P) {
     }
     int width = m;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) width = max(width, __shfl_xor_sync(0xffffffffu, width, o));
+    for (int o = 16; o > 0; o >>= 1) {
+        width = max(width, __shfl_xor_sync(0xffffffffu, width, o));
+        cmin  = min(cmin, __shfl_xor_sync(0xffffffffu, cmin, o));
+        cmax  = max(cmax, __shfl_xor_sync(0xffffffffu, cmax, o));
+    }
     width = min((width + 3) & ~3, P.K & ~3);
     for (int k = m; k < width; k++) {
         P.ell_col[SELL(k, s)] = s;
         P.ell_val[SELL(k, s)] = 0.0;
     }
-    if ((threadIdx.x & 31) == 0) P.ell_width[s >> 5] = width;
+    if ((threadIdx.x & 31) == 0) {
+        P.ell_width[s >> 5] = width;
+        P.ell_cmin[s >> 5]  = cmin; // column extent of the slice: the halo a row block needs (k_pcg.cu)
+        P.ell_cmax[s >> 5]  = cmax;
+    }
     P.ell_count[s] = m;
     P.diag[s]      = diag;
 }

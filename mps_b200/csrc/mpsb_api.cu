@@ -133,7 +133,7 @@ int mpsb_create(const mpsb_settings* settings, int64_t n, const int32_t* type, c
     Params& P = h->P;
     P.s = *settings;
     P.N = (int) n;
-    P.Np = (int) ((n + 31) / 32 * 32);
+    P.Np = (int) ((n + 255) / 256 * 256); // whole 32-row slices, and a whole number of them per rank for 1/2/4/8 ranks
     derive(P);
     const char* envk = getenv("MPSB_MAX_NEIGHBORS");
     P.K = envk ? atoi(envk) : (settings->dim == 2 ? 64 : 384);
@@ -182,7 +182,7 @@ int mpsb_create(const mpsb_settings* settings, int64_t n, const int32_t* type, c
     CKC(dalloc(&P.key, N)); CKC(dalloc(&P.key_alt, N)); CKC(dalloc(&P.val, N)); CKC(dalloc(&P.val_alt, N));
     CKC(dalloc(&P.cell_start, (size_t) P.numCells)); CKC(dalloc(&P.cell_end, (size_t) P.numCells));
     CKC(dalloc(&P.nbr_count, N)); CKC(dalloc(&P.nbr_idx, KN)); CKC(dalloc(&P.nbr_dist, KN));
-    CKC(dalloc(&P.ell_count, N)); CKC(dalloc(&P.ell_width, N / 32 + 1)); CKC(dalloc(&P.ell_col, KN)); CKC(dalloc(&P.ell_val, KN));
+    CKC(dalloc(&P.ell_count, N)); CKC(dalloc(&P.ell_width, N / 32 + 1)); CKC(dalloc(&P.ell_cmin, N / 32 + 1)); CKC(dalloc(&P.ell_cmax, N / 32 + 1)); CKC(dalloc(&P.ell_col, KN)); CKC(dalloc(&P.ell_val, KN));
     CKC(dalloc(&P.diag, N)); CKC(dalloc(&P.rhs, N));
     CKC(dalloc(&P.cg_r, N)); CKC(dalloc(&P.cg_p, N)); CKC(dalloc(&P.cg_ap, N)); CKC(dalloc(&P.cg_invdiag, N));
     CKC(dalloc(&P.parent, N)); CKC(dalloc(&P.mark, N));
@@ -219,13 +219,14 @@ int mpsb_destroy(mpsb_handle* h) {
     if (!h) return MPSB_OK;
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
+    mpsb_comm_release(h);
     Params& P = h->P;
     Sorted& S = P.S;
     Home& H   = P.H;
     void* ptrs[] = {S.x, S.y, S.z, S.u, S.v, S.w, S.u2, S.v2, S.w2, S.ax, S.ay, S.az, S.p, S.minp, S.ratio, S.type,
                     S.bc, S.id, H.pos, H.vel, H.acc, H.p, H.minp, H.ratio, H.type, H.bc, H.inv, P.key, P.key_alt,
                     P.val, P.val_alt, P.cell_start, P.cell_end, P.nbr_count, P.nbr_idx, P.nbr_dist, P.ell_count,
-                    P.ell_width, P.ell_col, P.ell_val, P.diag, P.rhs, P.cg_r, P.cg_p, P.cg_ap, P.cg_invdiag, P.cg_partials, P.cg_slice_pap,
+                    P.ell_width, P.ell_cmin, P.ell_cmax, P.ell_col, P.ell_val, P.diag, P.rhs, P.cg_r, P.cg_p, P.cg_ap, P.cg_invdiag, P.cg_partials, P.cg_slice_pap,
                     P.parent, P.mark, P.cand, P.cand_count, P.ev_ghost_id, P.ev_ghost_xyz, P.ev_uncon_id, P.stats,
                     h->block_hist};
     for (void* p : ptrs)
@@ -324,6 +325,7 @@ int mpsb_step(mpsb_handle* h, int want_number_density, mpsb_step_stats* stats) {
     mpsb_launch_dirichlet(h);
     CK(h, cudaEventRecord(E[6], st));
     mpsb_launch_pcg(h);
+    if (h->world > 1 && mpsb_comm_gather_pressure(h)) return h->sticky;
     CK(h, cudaEventRecord(E[7], st));
     mpsb_launch_pressure_post(h);
     mpsb_launch_gradient_move(h);                    // calcPressureGradient, moveParticlesWithPressureGradient
@@ -377,7 +379,10 @@ int mpsb_run_phase(mpsb_handle* h, int phase, mpsb_step_stats* stats) {
     case MPSB_PH_FLAGS_SOURCE: mpsb_launch_flags_source(h); break;
     case MPSB_PH_MATRIX: mpsb_launch_matrix(h); break;
     case MPSB_PH_DIRICHLET: mpsb_launch_dirichlet(h); break;
-    case MPSB_PH_SOLVE: mpsb_launch_pcg(h); break;
+    case MPSB_PH_SOLVE:
+        mpsb_launch_pcg(h);
+        if (h->world > 1 && mpsb_comm_gather_pressure(h)) return h->sticky;
+        break;
     case MPSB_PH_PRESSURE_POST: mpsb_launch_pressure_post(h); break;
     case MPSB_PH_GRADIENT_MOVE:
         CK(h, cudaMemsetAsync(&h->P.stats->n_ghosted, 0, sizeof(int), h->stream));
@@ -530,15 +535,3 @@ int mpsb_events(mpsb_handle* h, int kind, int32_t* ids, double* xyz, int capacit
 
 } // extern "C"
 
-// ---- multi-GPU attachment: implemented in mpsb_comm.cu when built with NCCL ------------------------
-#ifndef MPSB_WITH_NCCL
-extern "C" int mpsb_comm_unique_id(void* out128) {
-    (void) out128;
-    return MPSB_ERR_COMM;
-}
-extern "C" int mpsb_attach_comm(mpsb_handle* h, int rank, int world_size, const void* id) {
-    (void) rank; (void) world_size; (void) id;
-    if (h) snprintf(h->err, sizeof h->err, "library built without NCCL");
-    return MPSB_ERR_COMM;
-}
-#endif

@@ -1,0 +1,186 @@
+// mpsb_comm.cu — multi-GPU attachment of a handle (one process per GPU).
+//
+// NCCL (over NVLink 5 / NVSwitch) carries the bulk, once-per-step transfers: the bootstrap all-gather of
+// the CUDA IPC handles and the all-gather of the solved pressure row blocks. The Krylov iteration itself
+// never calls NCCL: its scalar reductions, barriers and halo rows move through peer-mapped HBM inside the
+// persistent PCG kernel (k_pcg.cu, pcg_kernel<true>), which is what the buffers exchanged here are for.
+//
+// NCCL is bound at run time (dlopen of libnccl.so.2: the copy torch already loaded when the host is
+// Python, the system one for the C++ host), so a single-GPU user needs no NCCL at all.
+// The reference has no counterpart: it is a single process.
+#include "mpsb_internal.cuh"
+
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include <cstdio>
+#include <cstring>
+
+namespace {
+
+struct NcclApi {
+    void* dl = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId*)                                                        = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int)                                 = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t)                                                           = nullptr;
+    ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t)   = nullptr;
+    const char* (*GetErrorString)(ncclResult_t)                                                       = nullptr;
+    bool ok = false;
+};
+
+NcclApi& nccl() {
+    static NcclApi api;
+    if (api.dl) return api;
+    const char* names[] = {"libnccl.so.2", "libnccl.so"};
+    for (const char* nm : names) {
+        api.dl = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+        if (api.dl) break;
+    }
+    if (!api.dl) return api;
+    api.GetUniqueId    = (decltype(api.GetUniqueId)) dlsym(api.dl, "ncclGetUniqueId");
+    api.CommInitRank   = (decltype(api.CommInitRank)) dlsym(api.dl, "ncclCommInitRank");
+    api.CommDestroy    = (decltype(api.CommDestroy)) dlsym(api.dl, "ncclCommDestroy");
+    api.AllGather      = (decltype(api.AllGather)) dlsym(api.dl, "ncclAllGather");
+    api.GetErrorString = (decltype(api.GetErrorString)) dlsym(api.dl, "ncclGetErrorString");
+    api.ok = api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.AllGather && api.GetErrorString;
+    return api;
+}
+
+struct MpsbComm {
+    ncclComm_t comm = nullptr;
+    void* inbox     = nullptr;                 // local; peers map it
+    void* staging   = nullptr;                 // device buffer for the handle all-gather
+    void* peer_inbox[MPSB_MAX_RANKS] = {};     // cudaIpcOpenMemHandle mappings (null for the own rank)
+    void* peer_p[MPSB_MAX_RANKS]     = {};
+};
+
+constexpr size_t INBOX_BYTES = 4096;
+constexpr size_t INBOX_RED   = 0;                                          // double[2][MAX][4]
+constexpr size_t INBOX_FLAG  = sizeof(double) * 2 * MPSB_MAX_RANKS * 4;    // u64[MAX]
+constexpr size_t INBOX_ARRIVE = INBOX_FLAG + sizeof(unsigned long long) * MPSB_MAX_RANKS;
+constexpr size_t INBOX_EPOCH  = INBOX_ARRIVE + 64;
+
+struct HandlePair {
+    cudaIpcMemHandle_t inbox;
+    cudaIpcMemHandle_t p;
+};
+
+int fail(mpsb_handle* h, const char* what, const char* detail) {
+    snprintf(h->err, sizeof h->err, "mpsb_attach_comm: %s (%s)", what, detail ? detail : "");
+    h->sticky = MPSB_ERR_COMM;
+    return MPSB_ERR_COMM;
+}
+
+} // namespace
+
+extern "C" int mpsb_comm_unique_id(void* out128) {
+    if (!out128) return MPSB_ERR_ARG;
+    NcclApi& N = nccl();
+    if (!N.ok) return MPSB_ERR_COMM;
+    ncclUniqueId id;
+    if (N.GetUniqueId(&id) != ncclSuccess) return MPSB_ERR_COMM;
+    static_assert(sizeof(id) == 128, "ncclUniqueId is 128 bytes");
+    memcpy(out128, &id, 128);
+    return MPSB_OK;
+}
+
+extern "C" int mpsb_attach_comm(mpsb_handle* h, int rank, int world_size, const void* id128) {
+    if (!h) return MPSB_ERR_ARG;
+    if (h->sticky) return h->sticky;
+    if (world_size == 1) return MPSB_OK;
+    Params& P = h->P;
+    if (!id128 || rank < 0 || rank >= world_size || world_size > MPSB_MAX_RANKS || (P.Np / 32) % world_size != 0 ||
+        h->comm) {
+        snprintf(h->err, sizeof h->err, "mpsb_attach_comm: bad rank/world (%d/%d; supported world sizes: 1, 2, 4, 8) "
+                 "or already attached", rank, world_size);
+        return MPSB_ERR_ARG;
+    }
+    NcclApi& N = nccl();
+    if (!N.ok) return fail(h, "libnccl.so.2 not found", dlerror());
+#define CKA(call)                                                                                  \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess) return fail(h, #call, cudaGetErrorString(e_));                      \
+    } while (0)
+#define CKN(call)                                                                                  \
+    do {                                                                                           \
+        ncclResult_t r_ = (call);                                                                  \
+        if (r_ != ncclSuccess) return fail(h, #call, N.GetErrorString(r_));                        \
+    } while (0)
+    CKA(cudaSetDevice(h->device));
+    MpsbComm* C = new MpsbComm();
+    h->comm     = C;
+    ncclUniqueId id;
+    memcpy(&id, id128, 128);
+    CKN(N.CommInitRank(&C->comm, world_size, id, rank));
+    CKA(cudaMalloc(&C->inbox, INBOX_BYTES));
+    CKA(cudaMemset(C->inbox, 0, INBOX_BYTES));
+    CKA(cudaMalloc(&C->staging, sizeof(HandlePair) * world_size));
+    HandlePair mine;
+    CKA(cudaIpcGetMemHandle(&mine.inbox, C->inbox));
+    CKA(cudaIpcGetMemHandle(&mine.p, P.cg_p));
+    CKA(cudaMemcpy((char*) C->staging + sizeof(HandlePair) * rank, &mine, sizeof mine, cudaMemcpyHostToDevice));
+    CKA(cudaStreamSynchronize(h->stream));
+    // the all-gather also orders every rank's inbox memset before any peer's first remote store
+    CKN(N.AllGather((char*) C->staging + sizeof(HandlePair) * rank, C->staging, sizeof(HandlePair), ncclChar, C->comm,
+                    h->stream));
+    CKA(cudaStreamSynchronize(h->stream));
+    HandlePair all[MPSB_MAX_RANKS];
+    CKA(cudaMemcpy(all, C->staging, sizeof(HandlePair) * world_size, cudaMemcpyDeviceToHost));
+    PeerLinks& L = P.L;
+    memset(&L, 0, sizeof L);
+    for (int q = 0; q < world_size; q++) {
+        void *ib = C->inbox, *pp = P.cg_p;
+        if (q != rank) {
+            CKA(cudaIpcOpenMemHandle(&C->peer_inbox[q], all[q].inbox, cudaIpcMemLazyEnablePeerAccess));
+            CKA(cudaIpcOpenMemHandle(&C->peer_p[q], all[q].p, cudaIpcMemLazyEnablePeerAccess));
+            ib = C->peer_inbox[q];
+            pp = C->peer_p[q];
+        }
+        L.peer_red[q]  = (double*) ((char*) ib + INBOX_RED);
+        L.peer_flag[q] = (unsigned long long*) ((char*) ib + INBOX_FLAG);
+        L.peer_p[q]    = (double*) pp;
+    }
+    L.red    = (double*) ((char*) C->inbox + INBOX_RED);
+    L.flag   = (unsigned long long*) ((char*) C->inbox + INBOX_FLAG);
+    L.arrive = (unsigned long long*) ((char*) C->inbox + INBOX_ARRIVE);
+    L.epoch  = (unsigned long long*) ((char*) C->inbox + INBOX_EPOCH);
+    L.rank   = rank;
+    L.world  = world_size;
+    h->rank  = rank;
+    h->world = world_size;
+#undef CKA
+#undef CKN
+    return MPSB_OK;
+}
+
+// After the solve every rank holds its own row block of the pressure; the rest of the step works on the
+// whole vector, so the blocks are all-gathered in place over NCCL.
+int mpsb_comm_gather_pressure(mpsb_handle* h) {
+    if (!h->comm || h->world <= 1) return MPSB_OK;
+    MpsbComm* C = (MpsbComm*) h->comm;
+    NcclApi& N  = nccl();
+    Params& P   = h->P;
+    size_t rows = (size_t) (P.Np / h->world);
+    ncclResult_t r = N.AllGather(P.S.p + rows * h->rank, P.S.p, rows, ncclDouble, C->comm, h->stream);
+    if (r != ncclSuccess) {
+        snprintf(h->err, sizeof h->err, "ncclAllGather(pressure): %s", N.GetErrorString(r));
+        h->sticky = MPSB_ERR_COMM;
+        return MPSB_ERR_COMM;
+    }
+    return MPSB_OK;
+}
+
+void mpsb_comm_release(mpsb_handle* h) {
+    if (!h || !h->comm) return;
+    MpsbComm* C = (MpsbComm*) h->comm;
+    for (int q = 0; q < MPSB_MAX_RANKS; q++) {
+        if (C->peer_inbox[q]) cudaIpcCloseMemHandle(C->peer_inbox[q]);
+        if (C->peer_p[q]) cudaIpcCloseMemHandle(C->peer_p[q]);
+    }
+    if (C->comm && nccl().ok) nccl().CommDestroy(C->comm);
+    if (C->staging) cudaFree(C->staging);
+    if (C->inbox) cudaFree(C->inbox);
+    delete C;
+    h->comm = nullptr;
+}

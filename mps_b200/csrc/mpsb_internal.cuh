@@ -55,6 +55,26 @@ struct Home {
     int *inv;                // particle id -> sorted index (valid after a build)
 };
 
+// Multi-GPU view of the PPE solve (mpsb_comm.cu). One process per GPU; rank g owns the
+// contiguous block of 32-row slices [g, g+1) * Np/32/world of the SORTED order, i.e. a y-slab of the cell
+// grid. Peers write straight into each other's HBM over NVLink/NVSwitch (buffers mapped with CUDA IPC):
+// reduction partials and epoch flags into the INBOX, and the halo rows of the search direction p into
+// the peer's own p vector at their natural row index. world == 1: unused.
+#define MPSB_MAX_RANKS 8
+struct PeerLinks {
+    int rank, world;
+    // my inbox (one allocation; peers hold a mapping of it)
+    double* red;                 // [2][MPSB_MAX_RANKS][4]: per-rank partials, double-buffered by epoch parity
+    unsigned long long* flag;    // [MPSB_MAX_RANKS]: exchange epoch each rank has reached
+    // local only (same allocation, never written by peers)
+    unsigned long long* arrive;  // CTA arrival counter of the running solve (zeroed by the host per launch)
+    unsigned long long* epoch;   // exchanges completed so far, monotonic across solves
+    // peers' inboxes and p vectors (entry [rank] is the local one)
+    double* peer_red[MPSB_MAX_RANKS];
+    unsigned long long* peer_flag[MPSB_MAX_RANKS];
+    double* peer_p[MPSB_MAX_RANKS];
+};
+
 // Everything a kernel needs, passed by value.
 struct Params {
     mpsb_settings s;
@@ -86,6 +106,7 @@ struct Params {
     // PPE: ELL off-diagonals + diagonal + rhs; CG vectors
     int *ell_count;            // Np  true off-diagonal count of the row
     int *ell_width;            // Np/32  padded slot count of the slice (multiple of 4; padding = (col row, val 0))
+    int *ell_cmin, *ell_cmax;  // Np/32  smallest / largest column of the slice (halo extent of a row block)
     int *ell_col;              // K*Np
     double *ell_val;           // K*Np
     double *diag, *rhs;        // N
@@ -103,6 +124,7 @@ struct Params {
     int *ev_ghost_id; double *ev_ghost_xyz; int *ev_uncon_id; int ev_cap;
     DevStats* stats;
     int* n_active; // == &stats->n_active
+    PeerLinks L;
 };
 
 struct mpsb_handle {
@@ -124,7 +146,7 @@ struct mpsb_handle {
     int sticky;
     // scratch for the radix sort
     int* block_hist; int block_hist_cap;
-    void* comm; int rank, world; // multi-GPU (mpsb_comm.cu)
+    void* comm; int rank, world; // multi-GPU (mpsb_comm.cu): MpsbComm*, mirrors P.L.rank / P.L.world
     // host staging for inspection calls
 };
 
@@ -144,6 +166,8 @@ void mpsb_launch_dirichlet(mpsb_handle* h);
 void mpsb_launch_pressure_post(mpsb_handle* h);
 void mpsb_launch_pcg(mpsb_handle* h);                   // k_pcg.cu
 int mpsb_pcg_configure(mpsb_handle* h);
+int mpsb_comm_gather_pressure(mpsb_handle* h);          // mpsb_comm.cu: all-gather the solved row blocks of p
+void mpsb_comm_release(mpsb_handle* h);
 
 #define MPSB_LAUNCH(h, kernel, grid, block, smem, ...)                                   \
     do {                                                                                 \

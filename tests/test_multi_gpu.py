@@ -1,0 +1,87 @@
+"""Multi-GPU path: host-side logic on CPU (gloo, world size 2) and, with >= 2 GPUs, the split PPE solve
+against the single-GPU solve (tools/multi_gpu_check.py, one process per GPU over NCCL/NVLink)."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+from mps_b200 import capi
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_row_blocks_partition_the_padded_rows():
+    for n in (1, 458, 2958, 6146, 4041990):
+        np_rows = capi.padded_rows(n)
+        assert np_rows % 256 == 0 and 0 <= np_rows - n < 256
+        for world in (1, 2, 4, 8):
+            edges = [capi.row_block(np_rows, r, world) for r in range(world)]
+            assert edges[0][0] == 0 and edges[-1][1] == np_rows
+            for (a, b), (c, d) in zip(edges, edges[1:]):
+                assert b == c and (b - a) == (d - c) and a % 32 == 0
+    with pytest.raises(ValueError):
+        capi.row_block(256, 0, 3)
+    with pytest.raises(ValueError):
+        capi.row_block(100, 0, 2)
+
+
+def _gloo_worker(rank, world, port, out):
+    import torch.distributed as dist
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    calls = []
+
+    def make():
+        calls.append(rank)
+        return bytes(range(128))
+
+    uid = capi.distribute_unique_id(rank, make)
+    ok = uid == bytes(range(128)) and calls == ([0] if rank == 0 else [])
+    # a malformed id must be rejected on every rank
+    try:
+        capi.distribute_unique_id(rank, lambda: b"short")
+        ok = False
+    except ValueError:
+        pass
+    with open(os.path.join(out, f"r{rank}"), "w") as f:
+        f.write("ok" if ok else "bad")
+    dist.destroy_process_group()
+
+
+def test_unique_id_distribution_gloo_world2(tmp_path):
+    import torch.multiprocessing as mp
+
+    port = 29500 + os.getpid() % 400
+    mp.spawn(_gloo_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    assert [open(tmp_path / f"r{r}").read() for r in range(2)] == ["ok", "ok"]
+
+
+def _gpu_count():
+    try:
+        import torch
+
+        return torch.cuda.device_count()
+    except Exception:
+        return 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case,steps", [("dambreak", 6), ("dambreak_fine", 4), ("nx=400", 2)])
+def test_split_solve_matches_single_gpu(case, steps):
+    n = _gpu_count()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    world = 4 if n >= 4 and case != "dambreak" else 2
+    port = 29600 + os.getpid() % 300
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+           "--master-addr", "127.0.0.1", "--master-port", str(port),
+           os.path.join(ROOT, "tools", "multi_gpu_check.py"), case, str(steps)]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    lines = [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
+    assert r.returncode == 0 and lines, r.stdout[-2000:] + r.stderr[-2000:]
+    rep = json.loads(lines[-1])
+    assert rep["ok"] and rep["ranks_bit_identical"] and rep["flags_equal"], rep
