@@ -35,16 +35,31 @@
 
 namespace cg = cooperative_groups;
 
-#ifndef PCG_EXP
-#define PCG_EXP 0
+#ifndef PCG_PIPE
+#define PCG_PIPE 0   // 1: software-pipelined sweep-A consumer (gathers of the next stage ahead of the FMAs); measured slower
+#endif
+#ifndef PCG_NSTAGES
+#define PCG_NSTAGES 2
+#endif
+#ifndef PCG_NCH
+#define PCG_NCH 12
+#endif
+#ifndef PCG_NWARPS
+#define PCG_NWARPS 20
+#endif
+#ifndef PCG_NBATCH
+#define PCG_NBATCH 2
+#endif
+#ifndef PCG_EVICT
+#define PCG_EVICT 0  // 1: matrix bulk copies carry an L2 evict_first policy (the matrix is read once per sweep)
 #endif
 
 namespace {
 
-constexpr int PCG_WARPS   = 16;            // warps per CTA (one CTA per SM)
+constexpr int PCG_WARPS   = PCG_NWARPS;    // warps per CTA (one CTA per SM)
 constexpr int PCG_THREADS = PCG_WARPS * 32;
-constexpr int PCG_STAGES  = 3;             // ring depth per warp
-constexpr int PCG_CH      = 8;             // slots per stage (multiple of 4): 8 * 384 B = 3 KB + diag
+constexpr int PCG_STAGES  = PCG_NSTAGES;   // ring depth per warp
+constexpr int PCG_CH      = PCG_NCH;       // slots per stage (multiple of 4): 8 * 384 B = 3 KB + diag
 // one stage: CH slots of 32 values, the slice's 32 diagonals, CH slots of 32 columns
 struct __align__(128) Stage {
     double val[PCG_CH * 32];
@@ -96,6 +111,20 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned by
                      smem_u32(dst)),
                  "l"(src), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
+}
+
+__device__ __forceinline__ unsigned long long l2_evict_first_policy() {
+    unsigned long long pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ void bulk_g2s_hint(void* dst, const void* src, unsigned bytes, unsigned long long* bar,
+                                              unsigned long long pol) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(
+            smem_u32(dst)),
+        "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(pol)
+        : "memory");
 }
 
 // Deterministic block-wide reduction of two values; result broadcast to every thread.
@@ -240,7 +269,7 @@ struct Pipe {
     unsigned consumed;
 };
 
-constexpr int PCG_BATCH = 2; // slices taken from the global queue per atomic
+constexpr int PCG_BATCH = PCG_NBATCH; // slices taken from the global queue per atomic
 
 // Sweep A for the calling warp: ap = A p. Slices are handed out DYNAMICALLY (a global ticket counter,
 // PCG_BATCH slices per ticket, tickets fetched two ahead so neither the atomic nor the width loads sit
@@ -253,6 +282,9 @@ __device__ __forceinline__ void spmv_sweep(const Params& P, Smem& sm, Pipe& pipe
                                            double* ap, unsigned* ticket, double* slice_pap) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const size_t K = (size_t) P.K;
+#if PCG_EVICT
+    const unsigned long long evict_first = l2_evict_first_policy();
+#endif
     auto take = [&]() -> int { // lane 0 holds the result; shuffled when needed
         int v = 0;
         if (lane == 0) v = sbeg + (int) atomicAdd(ticket, (unsigned) PCG_BATCH);
@@ -281,8 +313,13 @@ __device__ __forceinline__ void spmv_sweep(const Params& P, Smem& sm, Pipe& pipe
             if (first) bulk_g2s(S.diag, P.diag + (size_t) slice * 32, 256u, bar);
             if (nsl > 0) {
                 const size_t off = ((size_t) slice * K + (size_t) pk) * 32;
+#if PCG_EVICT
+                bulk_g2s_hint(S.val, P.ell_val + off, (unsigned) nsl * 256u, bar, evict_first);
+                bulk_g2s_hint(S.col, P.ell_col + off, (unsigned) nsl * 128u, bar, evict_first);
+#else
                 bulk_g2s(S.val, P.ell_val + off, (unsigned) nsl * 256u, bar);
                 bulk_g2s(S.col, P.ell_col + off, (unsigned) nsl * 128u, bar);
+#endif
             }
         }
         pipe.issued++;
@@ -302,6 +339,76 @@ __device__ __forceinline__ void spmv_sweep(const Params& P, Smem& sm, Pipe& pipe
     };
     double sum = 0.0, pr = 0.0;
     int row = 0;
+#if PCG_PIPE
+    // Software-pipelined consumer: the column loads and p[col] gathers of stage j+1 are issued BEFORE the
+    // multiply-adds of stage j, so the gather latency (L1 miss -> L2 under a saturated HBM stream) overlaps
+    // the arithmetic, the ring bookkeeping and the TMA issue instead of heading every stage's dependent
+    // chain. Two register sets (ga/gb) alternate; the summation order per row is unchanged (slot order).
+    auto fetch = [&](unsigned serial, double (&g)[PCG_CH], double& gpr) {
+        const unsigned st = serial % PCG_STAGES, parity = (serial / PCG_STAGES) & 1u;
+        const StageMeta m = sm.meta[warp][st];
+        const Stage& S    = sm.stage[warp][st];
+        if (m.first) gpr = p[m.slice * 32 + lane];
+        mbar_wait(&sm.full[warp][st], parity);
+#pragma unroll
+        for (int k = 0; k < PCG_CH; k++) {
+            const int c = k < m.nslots ? S.col[k * 32 + lane] : 0;
+            g[k] = p[c];
+        }
+    };
+    auto compute = [&](double (&g)[PCG_CH], double gpr) {
+        const unsigned st = pipe.consumed % PCG_STAGES;
+        const StageMeta m = sm.meta[warp][st];
+        const Stage& S    = sm.stage[warp][st];
+        if (m.first) {
+            row = m.slice * 32 + lane;
+            pr  = gpr;
+            sum = S.diag[lane] * pr;
+        }
+#pragma unroll
+        for (int k = 0; k < PCG_CH; k += 4) {
+            if (k < m.nslots) {
+                double v0 = S.val[(k + 0) * 32 + lane], v1 = S.val[(k + 1) * 32 + lane];
+                double v2 = S.val[(k + 2) * 32 + lane], v3 = S.val[(k + 3) * 32 + lane];
+                sum += v0 * g[k + 0]; sum += v1 * g[k + 1]; sum += v2 * g[k + 2]; sum += v3 * g[k + 3];
+            }
+        }
+        if (m.last) {
+            ap[row] = sum;
+            double v = pr * sum;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            if (lane == 0) slice_pap[m.slice] = v;
+        }
+        __syncwarp(); // every lane is done with the stage before lane 0 refills it
+        pipe.consumed++;
+    };
+    double ga[PCG_CH], gb[PCG_CH], gpa = 0.0, gpb = 0.0;
+    while (produce()) {}
+    if (pipe.consumed == pipe.issued) return;
+    __syncwarp(); // lane 0's meta of freshly issued stages is visible to the warp
+    fetch(pipe.consumed, ga, gpa);
+    for (;;) {
+        bool ahead = pipe.consumed + 1u < pipe.issued;
+        if (ahead) fetch(pipe.consumed + 1u, gb, gpb);
+        compute(ga, gpa);
+        while (produce()) {}
+        __syncwarp();
+        if (!ahead) {
+            if (pipe.consumed == pipe.issued) break;
+            fetch(pipe.consumed, gb, gpb);
+        }
+        ahead = pipe.consumed + 1u < pipe.issued;
+        if (ahead) fetch(pipe.consumed + 1u, ga, gpa);
+        compute(gb, gpb);
+        while (produce()) {}
+        __syncwarp();
+        if (!ahead) {
+            if (pipe.consumed == pipe.issued) break;
+            fetch(pipe.consumed, ga, gpa);
+        }
+    }
+#else
     for (;;) {
         while (produce()) {}
         if (pipe.consumed == pipe.issued) break;
@@ -315,15 +422,18 @@ __device__ __forceinline__ void spmv_sweep(const Params& P, Smem& sm, Pipe& pipe
         }
         mbar_wait(&sm.full[warp][st], parity);
         if (m.first) sum = S.diag[lane] * pr;
+        double g[PCG_CH]; // all gathers of the stage in flight together
+#pragma unroll
+        for (int k = 0; k < PCG_CH; k++) {
+            const int c = k < m.nslots ? S.col[k * 32 + lane] : 0;
+            g[k] = p[c];
+        }
 #pragma unroll
         for (int k = 0; k < PCG_CH; k += 4) {
             if (k < m.nslots) {
-                int c0 = S.col[(k + 0) * 32 + lane], c1 = S.col[(k + 1) * 32 + lane];
-                int c2 = S.col[(k + 2) * 32 + lane], c3 = S.col[(k + 3) * 32 + lane];
-                double p0 = p[c0], p1 = p[c1], p2 = p[c2], p3 = p[c3];
                 double v0 = S.val[(k + 0) * 32 + lane], v1 = S.val[(k + 1) * 32 + lane];
                 double v2 = S.val[(k + 2) * 32 + lane], v3 = S.val[(k + 3) * 32 + lane];
-                sum += v0 * p0; sum += v1 * p1; sum += v2 * p2; sum += v3 * p3;
+                sum += v0 * g[k + 0]; sum += v1 * g[k + 1]; sum += v2 * g[k + 2]; sum += v3 * g[k + 3];
             }
         }
         if (m.last) {
@@ -336,6 +446,7 @@ __device__ __forceinline__ void spmv_sweep(const Params& P, Smem& sm, Pipe& pipe
         __syncwarp(); // every lane is done with the stage before lane 0 refills it
         pipe.consumed++;
     }
+#endif
 }
 
 // MULTI = false: one GPU, rows [0, n). MULTI = true: this rank's row block; see the file header.
