@@ -1,0 +1,57 @@
+// host_selftest.cpp — CPU-only driver for the host code (no device calls), used by tests/test_host.py:
+//   host_selftest settings <settings.yml>            parsed Settings + RefValues, one "key value" per line (%.17g)
+//   host_selftest reexport <settings.yml> <out dir>  input CSV -> particles -> out/particles.csv, out/particles.vtu
+//   host_selftest float <style> <value>...           spelling of doubles (style: fixed6 | gcc5)
+#include "exporter.hpp"
+#include "mps.hpp"
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+
+static void kv(const char* k, double v) { std::printf("%s %.17g\n", k, v); }
+
+int main(int argc, char** argv) {
+    if (argc < 3) {
+        std::fprintf(stderr, "usage: host_selftest settings|reexport|float ...\n");
+        return 2;
+    }
+    const std::string mode = argv[1];
+    if (mode == "float") {
+        auto style = std::strcmp(argv[2], "gcc5") == 0 ? csv_io::FloatStyle::Trunc5Gcc : csv_io::FloatStyle::Fixed6;
+        for (int i = 3; i < argc; i++) std::printf("%s\n", csv_io::formatFloat(std::strtod(argv[i], nullptr), style).c_str());
+        return 0;
+    }
+    MPS mps{std::filesystem::path(argv[2])};
+    const Settings& s = mps.settings;
+    if (mode == "settings") {
+        kv("dim", s.dim); kv("particle_distance", s.particleDistance); kv("dt", s.dt); kv("finish_time", s.finishTime);
+        kv("output_interval", s.outputInterval); kv("cfl_condition", s.cflCondition);
+        kv("domain_min_x", s.domain.x.min); kv("domain_max_x", s.domain.x.max); kv("domain_min_y", s.domain.y.min);
+        kv("domain_max_y", s.domain.y.max); kv("domain_min_z", s.domain.z.min); kv("domain_max_z", s.domain.z.max);
+        kv("density", s.density); kv("kinematic_viscosity", s.kinematicViscosity);
+        kv("gravity_x", s.gravity.x()); kv("gravity_y", s.gravity.y()); kv("gravity_z", s.gravity.z());
+        kv("re_pressure", s.effectiveRadius.pressure); kv("re_viscosity", s.effectiveRadius.viscosity);
+        kv("re_surface", s.effectiveRadius.surfaceDetection); kv("re_max", s.effectiveRadius.max);
+        kv("surface_threshold", s.thresholdForSurfaceDetection);
+        kv("quasi_compressibility_on", s.quasiCompressibility.on); kv("compressibility", s.quasiCompressibility.compressibility);
+        kv("higher_order_source_on", s.higherOrderSourceTerm.on); kv("higher_order_gamma", s.higherOrderSourceTerm.gamma);
+        kv("relaxation_coefficient", s.relaxationCoefficientForPressure);
+        kv("collision_distance", s.collisionDistance); kv("restitution", s.coefficientOfRestitution);
+        kv("n0_pressure", mps.refValuesPressure().initialNumberDensity); kv("lambda_pressure", mps.refValuesPressure().lambda);
+        kv("n0_viscosity", mps.refValuesViscosity().initialNumberDensity); kv("lambda_viscosity", mps.refValuesViscosity().lambda);
+        kv("n0_surface", mps.refValuesSurfaceDetection().initialNumberDensity); kv("lambda_surface", mps.refValuesSurfaceDetection().lambda);
+        std::printf("input_csv_path %s\n", s.inputCsvPath.string().c_str());
+        return 0;
+    }
+    if (mode == "reexport" && argc >= 4) {
+        double t = mps.loadParticlesOnly();
+        Exporter e;
+        e.toCsv(std::filesystem::path(argv[3]) / "particles.csv", mps.particles, t);
+        e.toVtu(std::filesystem::path(argv[3]) / "particles.vtu", mps.particles, t);
+        std::printf("particles %zu time %.17g\n", mps.particles.size(), t);
+        return 0;
+    }
+    return 2;
+}
