@@ -64,7 +64,7 @@ constexpr int PCG_CH      = PCG_NCH;       // slots per stage (multiple of 4): 8
 struct __align__(128) Stage {
     double val[PCG_CH * 32];
     double diag[32];
-    int col[PCG_CH * 32];
+    int col[PCG_CH * 32]; // 16-bit column mode: the first half holds short offsets from the slice's first row
 };
 struct __align__(16) StageMeta {
     int slice;
@@ -278,13 +278,11 @@ constexpr int PCG_BATCH = PCG_NBATCH; // slices taken from the global queue per 
 // into slice_pap[]; the caller sums that array in a fixed order. Rows of a slice beyond n carry diag 0 /
 // padding only and p = 0 there.
 // The sweep covers slices [sbeg, nslices) (a rank's row block; sbeg = 0 on one GPU).
+template <bool C16>
 __device__ __forceinline__ void spmv_sweep(const Params& P, Smem& sm, Pipe& pipe, int sbeg, int nslices, const double* p,
                                            double* ap, unsigned* ticket, double* slice_pap) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const size_t K = (size_t) P.K;
-#if PCG_EVICT
-    const unsigned long long evict_first = l2_evict_first_policy();
-#endif
     auto take = [&]() -> int { // lane 0 holds the result; shuffled when needed
         int v = 0;
         if (lane == 0) v = sbeg + (int) atomicAdd(ticket, (unsigned) PCG_BATCH);
@@ -309,17 +307,13 @@ __device__ __forceinline__ void spmv_sweep(const Params& P, Smem& sm, Pipe& pipe
             Stage& S = sm.stage[warp][st];
             sm.meta[warp][st] = StageMeta{slice, nsl, first ? 1 : 0, last ? 1 : 0};
             unsigned long long* bar = &sm.full[warp][st];
-            mbar_arrive_expect_tx(bar, (first ? 256u : 0u) + (unsigned) nsl * 384u);
+            mbar_arrive_expect_tx(bar, (first ? 256u : 0u) + (unsigned) nsl * (C16 ? 320u : 384u));
             if (first) bulk_g2s(S.diag, P.diag + (size_t) slice * 32, 256u, bar);
             if (nsl > 0) {
                 const size_t off = ((size_t) slice * K + (size_t) pk) * 32;
-#if PCG_EVICT
-                bulk_g2s_hint(S.val, P.ell_val + off, (unsigned) nsl * 256u, bar, evict_first);
-                bulk_g2s_hint(S.col, P.ell_col + off, (unsigned) nsl * 128u, bar, evict_first);
-#else
-                bulk_g2s(S.val, P.ell_val + off, (unsigned) nsl * 256u, bar);
-                bulk_g2s(S.col, P.ell_col + off, (unsigned) nsl * 128u, bar);
-#endif
+bulk_g2s(S.val, P.ell_val + off, (unsigned) nsl * 256u, bar);
+                if (C16) bulk_g2s(S.col, P.ell_col16 + off, (unsigned) nsl * 64u, bar);
+                else bulk_g2s(S.col, P.ell_col + off, (unsigned) nsl * 128u, bar);
             }
         }
         pipe.issued++;
@@ -352,7 +346,11 @@ __device__ __forceinline__ void spmv_sweep(const Params& P, Smem& sm, Pipe& pipe
         mbar_wait(&sm.full[warp][st], parity);
 #pragma unroll
         for (int k = 0; k < PCG_CH; k++) {
-            const int c = k < m.nslots ? S.col[k * 32 + lane] : 0;
+            int c = 0;
+            if (k < m.nslots) {
+                if (C16) c = m.slice * 32 + (int) reinterpret_cast<const short*>(S.col)[k * 32 + lane];
+                else c = S.col[k * 32 + lane];
+            }
             g[k] = p[c];
         }
     };
@@ -425,7 +423,11 @@ __device__ __forceinline__ void spmv_sweep(const Params& P, Smem& sm, Pipe& pipe
         double g[PCG_CH]; // all gathers of the stage in flight together
 #pragma unroll
         for (int k = 0; k < PCG_CH; k++) {
-            const int c = k < m.nslots ? S.col[k * 32 + lane] : 0;
+            int c = 0;
+            if (k < m.nslots) {
+                if (C16) c = m.slice * 32 + (int) reinterpret_cast<const short*>(S.col)[k * 32 + lane];
+                else c = S.col[k * 32 + lane];
+            }
             g[k] = p[c];
         }
 #pragma unroll
@@ -478,6 +480,9 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
     const int sl_lo = row_lo >> 5, sl_hi = (act_hi + 31) >> 5; // slices with at least one active row
     Xchg xs{0ull, 0ull};
     if (MULTI) xs.epoch = *P.L.epoch;
+    // columns stream as 16-bit offsets from the slice's first row (10 B per entry instead of 12) unless the
+    // assembly met an offset that does not fit (matrix_kernel sets ell_wide); uniform over the grid
+    const bool col16 = *P.ell_wide == 0;
 
     if (threadIdx.x < PCG_WARPS * PCG_STAGES) mbar_init(&sm.full[0][0] + threadIdx.x, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -575,7 +580,8 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
     while (!done && it < maxIters) {
         // ---- sweep A: ap = A p, p.ap ----
         unsigned* ticket = tickets + (it & 1);
-        spmv_sweep(P, sm, pipe, sl_lo, sl_hi, p, ap, ticket, P.cg_slice_pap);
+        if (col16) spmv_sweep<true>(P, sm, pipe, sl_lo, sl_hi, p, ap, ticket, P.cg_slice_pap);
+        else spmv_sweep<false>(P, sm, pipe, sl_lo, sl_hi, p, ap, ticket, P.cg_slice_pap);
         __syncthreads();
         PCG_TICK(0);
         grid.sync();

@@ -5,6 +5,8 @@
 //   clamp_kernel / min_pressure_kernel : removeNegativePressure + setMinimumPressure (:472-503)
 #include "mpsb_internal.cuh"
 
+#include <cstdlib>
+
 namespace {
 
 // Boundary-condition flag for every slot and, for the standard source term, b_i in the same pass
@@ -72,7 +74,7 @@ __global__ void __launch_bounds__(256) source_ho_kernel(Params P) {
 __global__ void __launch_bounds__(256) matrix_kernel(Params P) {
     int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= P.Np) return; // Np is a multiple of 32: whole warps leave together
-    int m = 0, cmin = s, cmax = s;
+    int m = 0, cmin = s, cmax = s, wide = 0;
     double diag = 0.0;
     if (s < *P.n_active && P.S.bc[s] == MPSB_BC_INNER) {
         const double re = P.s.re_pressure;
@@ -88,6 +90,9 @@ __global__ void __launch_bounds__(256) matrix_kernel(Params P) {
                 if (bcj == MPSB_BC_INNER) {
                     P.ell_col[SELL(m, s)] = j;
                     P.ell_val[SELL(m, s)] = -a;
+                    const int off = j - (s & ~31); // 16-bit form: offset from the slice's first row
+                    P.ell_col16[SELL(m, s)] = (short) off;
+                    if (off < -32768 || off > 32767) wide = 1;
                     cmin = min(cmin, j);
                     cmax = max(cmax, j);
                     m++;
@@ -106,9 +111,11 @@ __global__ void __launch_bounds__(256) matrix_kernel(Params P) {
     }
     width = min((width + 3) & ~3, P.K & ~3);
     for (int k = m; k < width; k++) {
-        P.ell_col[SELL(k, s)] = s;
-        P.ell_val[SELL(k, s)] = 0.0;
+        P.ell_col[SELL(k, s)]   = s;
+        P.ell_col16[SELL(k, s)] = (short) (s & 31);
+        P.ell_val[SELL(k, s)]   = 0.0;
     }
+    if (wide) *P.ell_wide = 1;
     if ((threadIdx.x & 31) == 0) {
         P.ell_width[s >> 5] = width;
         P.ell_cmin[s >> 5]  = cmin; // column extent of the slice: the halo a row block needs (k_pcg.cu)
@@ -214,6 +221,8 @@ void mpsb_launch_flags_source(mpsb_handle* h) {
 void mpsb_launch_matrix(mpsb_handle* h) {
     Params& P = h->P;
     cudaMemsetAsync(&P.stats->nnz, 0, sizeof(int), h->stream);
+    const char* force = getenv("MPSB_FORCE_WIDE_COLUMNS"); // tests: exercise the 32-bit column stream
+    cudaMemsetAsync(P.ell_wide, force && atoi(force) ? 0xFF : 0, sizeof(int), h->stream);
     MPSB_LAUNCH(h, matrix_kernel, mpsb_div_up(P.Np, 256) , 256, 0, P);
 }
 

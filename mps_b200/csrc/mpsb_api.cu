@@ -183,6 +183,7 @@ int mpsb_create(const mpsb_settings* settings, int64_t n, const int32_t* type, c
     CKC(dalloc(&P.cell_start, (size_t) P.numCells)); CKC(dalloc(&P.cell_end, (size_t) P.numCells));
     CKC(dalloc(&P.nbr_count, N)); CKC(dalloc(&P.nbr_idx, KN)); CKC(dalloc(&P.nbr_dist, KN));
     CKC(dalloc(&P.ell_count, N)); CKC(dalloc(&P.ell_width, N / 32 + 1)); CKC(dalloc(&P.ell_cmin, N / 32 + 1)); CKC(dalloc(&P.ell_cmax, N / 32 + 1)); CKC(dalloc(&P.ell_col, KN)); CKC(dalloc(&P.ell_val, KN));
+    CKC(dalloc(&P.ell_col16, KN)); CKC(dalloc(&P.ell_wide, 1));
     CKC(dalloc(&P.diag, N)); CKC(dalloc(&P.rhs, N));
     CKC(dalloc(&P.cg_r, N)); CKC(dalloc(&P.cg_p, N)); CKC(dalloc(&P.cg_ap, N)); CKC(dalloc(&P.cg_invdiag, N));
     CKC(dalloc(&P.parent, N)); CKC(dalloc(&P.mark, N));
@@ -226,7 +227,7 @@ int mpsb_destroy(mpsb_handle* h) {
     void* ptrs[] = {S.x, S.y, S.z, S.u, S.v, S.w, S.u2, S.v2, S.w2, S.ax, S.ay, S.az, S.p, S.minp, S.ratio, S.type,
                     S.bc, S.id, H.pos, H.vel, H.acc, H.p, H.minp, H.ratio, H.type, H.bc, H.inv, P.key, P.key_alt,
                     P.val, P.val_alt, P.cell_start, P.cell_end, P.nbr_count, P.nbr_idx, P.nbr_dist, P.ell_count,
-                    P.ell_width, P.ell_cmin, P.ell_cmax, P.ell_col, P.ell_val, P.diag, P.rhs, P.cg_r, P.cg_p, P.cg_ap, P.cg_invdiag, P.cg_partials, P.cg_slice_pap,
+                    P.ell_width, P.ell_cmin, P.ell_cmax, P.ell_col, P.ell_col16, P.ell_wide, P.ell_val, P.diag, P.rhs, P.cg_r, P.cg_p, P.cg_ap, P.cg_invdiag, P.cg_partials, P.cg_slice_pap,
                     P.parent, P.mark, P.cand, P.cand_count, P.ev_ghost_id, P.ev_ghost_xyz, P.ev_uncon_id, P.stats,
                     h->block_hist};
     for (void* p : ptrs)

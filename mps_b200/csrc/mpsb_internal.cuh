@@ -108,6 +108,8 @@ struct Params {
     int *ell_width;            // Np/32  padded slot count of the slice (multiple of 4; padding = (col row, val 0))
     int *ell_cmin, *ell_cmax;  // Np/32  smallest / largest column of the slice (halo extent of a row block)
     int *ell_col;              // K*Np
+    short *ell_col16;          // K*Np  column - first row of the slice, when every such offset fits 16 bits
+    int *ell_wide;             // 1     set by the assembly when some offset does not fit: the solve then streams ell_col
     double *ell_val;           // K*Np
     double *diag, *rhs;        // N
     double *cg_r, *cg_p, *cg_ap, *cg_invdiag; // N

@@ -247,3 +247,22 @@ def test_scaled_dambreak_nonkrylov_phases_bitwise_and_cg_properties(nx):
         orc.phase(R.PH_SOLVE)
         assert U.rel_err(x, orc.get_state(["pressure"])["pressure"]) <= TOL
     dev.close()
+
+
+def test_16_bit_and_32_bit_column_streams_give_identical_solves(monkeypatch):
+    """The solve streams columns as 16-bit offsets from the slice's first row when they all fit, else as
+    int32 (matrix_kernel decides per assembly). Same arithmetic in the same order -> bitwise equal pressure,
+    iteration count and residual. MPSB_FORCE_WIDE_COLUMNS=1 forces the 32-bit stream."""
+    S, t, p, v = C.scaled_dambreak(200)
+    out = []
+    for force in ("0", "1"):
+        monkeypatch.setenv("MPSB_FORCE_WIDE_COLUMNS", force)
+        dev = capi.DeviceMPS(S, t, p, v)
+        dev.load_initial_state()
+        for name, dph, _ in PHASE_MAP[:8]:
+            dev.run_phase(dph)
+        st = dev.run_phase(capi.PH_SOLVE)
+        out.append((dev.download(["pressure"])["pressure"], st.cg_iterations, st.cg_rel_residual))
+        dev.close()
+    assert np.array_equal(out[0][0], out[1][0]) and out[0][1:] == out[1][1:]
+    assert np.abs(out[0][0]).max() > 0
