@@ -50,8 +50,8 @@ namespace cg = cooperative_groups;
 #ifndef PCG_NBATCH
 #define PCG_NBATCH 2
 #endif
-#ifndef PCG_EVICT
-#define PCG_EVICT 0  // 1: matrix bulk copies carry an L2 evict_first policy (the matrix is read once per sweep)
+#ifndef PCG_SPLIT_SYNC
+#define PCG_SPLIT_SYNC 0 // diagnostic: book the barrier/exchange after sweep B under B and after sweep C under C
 #endif
 
 namespace {
@@ -78,6 +78,7 @@ struct Smem {
     unsigned long long full[PCG_WARPS][PCG_STAGES];
     double red[66];
     int need[MPSB_MAX_RANKS][2]; // MULTI: my rows each peer reads, [lo, hi)
+    double xr[MPSB_MAX_RANKS][2]; // MULTI: every rank's pair of the last exchange
     int flag;                    // MULTI: this CTA arrived last at the running exchange
 };
 
@@ -88,9 +89,6 @@ __device__ __forceinline__ void mbar_init(unsigned long long* bar, int count) {
 }
 __device__ __forceinline__ void mbar_arrive_expect_tx(unsigned long long* bar, unsigned bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(unsigned long long* bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
     unsigned ok = 0, addr = smem_u32(bar), spins = 0;
@@ -111,20 +109,6 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned by
                      smem_u32(dst)),
                  "l"(src), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
-}
-
-__device__ __forceinline__ unsigned long long l2_evict_first_policy() {
-    unsigned long long pol;
-    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
-    return pol;
-}
-__device__ __forceinline__ void bulk_g2s_hint(void* dst, const void* src, unsigned bytes, unsigned long long* bar,
-                                              unsigned long long pol) {
-    asm volatile(
-        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(
-            smem_u32(dst)),
-        "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(pol)
-        : "memory");
 }
 
 // Deterministic block-wide reduction of two values; result broadcast to every thread.
@@ -200,65 +184,105 @@ struct Xchg {
     unsigned long long count; // exchanges completed in this launch
 };
 
-// One fused all-to-all + barrier over all CTAs of all ranks. Every CTA contributes (a, b); on return every
-// thread of every rank can read each rank's combined pair from its inbox (xchg_slot). Steps:
-//   1. CTA partials -> local array; fence.sys (publishes this CTA's earlier remote p stores too: the
-//      fence of thread 0 after the CTA barrier is cumulative); arrive on the local counter.
+// One fused all-to-all + barrier over all CTAs of all ranks. Every CTA contributes (a, b); on return
+// xr[q][0..1] (shared memory) holds rank q's combined pair on every CTA of every rank. Steps:
+//   1. CTA partials -> local array; fence; arrive on the local counter.
 //   2. The CTA that arrives last combines the partials in index order (deterministic, whoever is last) and
-//      stores the rank's pair into the inbox of every rank, then the epoch flag with release.sys.
-//   3. Every CTA waits until all W flags in its OWN inbox (local HBM, no NVLink polling) reach the epoch.
+//      stores the rank's pair into the inbox of every rank.
+//   3. Every CTA polls its OWN inbox (local HBM, no polling over NVLink) until all W ranks have delivered.
+// Two wire formats:
+//   XCHG_SUM / XCHG_MINMAX  carry data and nothing else has to be visible with them -> flag-in-data lines
+//       (each double travels as one 16-byte store {lo32, flag, hi32, flag}, flag = low 32 bits of the epoch;
+//       only 8-byte store atomicity is assumed). One NVLink one-way latency, no fence, no acknowledgement.
+//   XCHG_PUBLISH            carries no data but publishes the halo rows of p that sweep C stored into the
+//       peers' p vectors: every CTA fences at system scope before arriving, the last CTA stores the epoch flag
+//       with release.sys, readers poll it with acquire.sys.
 // It subsumes a grid-wide barrier. A rank that never arrives (crashed peer) trips the timeout -> trap,
 // which fails the launch loudly instead of hanging the box.
-template <bool MINMAX>
+enum { XCHG_SUM = 0, XCHG_MINMAX = 1, XCHG_PUBLISH = 2 };
+
+__device__ __forceinline__ void xchg_timeout(const Params& P, unsigned long long t0) {
+    if (global_timer_ns() - t0 > 20000000000ull) { // 20 s: a peer is gone
+        atomicOr(&P.stats->error_flags, 8);
+        __threadfence_system();
+        __trap();
+    }
+}
+
+template <int MODE>
 __device__ __forceinline__ void xchg_all(const Params& P, Xchg& xs, double a, double b, double* part0, double* part1,
-                                         double* sh, int* sflag) {
+                                         double* sh, int* sflag, double (*xr)[2]) {
+    constexpr bool MINMAX = MODE == XCHG_MINMAX;
     const PeerLinks& L = P.L;
     const int W = L.world, nblocks = gridDim.x;
     xs.epoch++;
     xs.count++;
-    block_sum2<MINMAX>(a, b, sh);
+    const unsigned fl = (unsigned) xs.epoch;
+    if (MODE != XCHG_PUBLISH) block_sum2<MINMAX>(a, b, sh);
+    else __syncthreads(); // all halo stores of the CTA precede thread 0's fence
     if (threadIdx.x == 0) {
-        part0[blockIdx.x] = a;
-        part1[blockIdx.x] = b;
-        __threadfence_system();
+        if (MODE != XCHG_PUBLISH) {
+            part0[blockIdx.x] = a;
+            part1[blockIdx.x] = b;
+            __threadfence();
+        } else {
+            __threadfence_system();
+        }
         unsigned long long t = atomicAdd(L.arrive, 1ull);
-        *sflag = (t + 1ull == xs.count * (unsigned long long) nblocks) ? 1 : 0;
+        const int last = (t + 1ull == xs.count * (unsigned long long) nblocks) ? 1 : 0;
+        if (last) {
+            if (MODE != XCHG_PUBLISH) __threadfence();
+            else __threadfence_system();
+        }
+        *sflag = last;
     }
     __syncthreads();
     if (*sflag) {
-        __threadfence_system();
-        double la = MINMAX ? DBL_MAX : 0.0, lb = MINMAX ? -DBL_MAX : 0.0;
-        for (int i = threadIdx.x; i < nblocks; i += PCG_THREADS) combine2<MINMAX>(la, lb, __ldcg(part0 + i), __ldcg(part1 + i));
-        block_sum2<MINMAX>(la, lb, sh);
-        if ((int) threadIdx.x < W) {
-            const int q = threadIdx.x;
-            double* dst = L.peer_red[q] + ((size_t) (xs.epoch & 1ull) * MPSB_MAX_RANKS + L.rank) * 4;
-            asm volatile("st.relaxed.sys.global.v2.f64 [%0], {%1, %2};" ::"l"(dst), "d"(la), "d"(lb) : "memory");
-            st_release_sys(L.peer_flag[q] + L.rank, xs.epoch);
+        if (MODE != XCHG_PUBLISH) {
+            double la = MINMAX ? DBL_MAX : 0.0, lb = MINMAX ? -DBL_MAX : 0.0;
+            for (int i = threadIdx.x; i < nblocks; i += PCG_THREADS) combine2<MINMAX>(la, lb, __ldcg(part0 + i), __ldcg(part1 + i));
+            block_sum2<MINMAX>(la, lb, sh);
+            if ((int) threadIdx.x < 2 * W) {
+                const int q = threadIdx.x >> 1, ln = threadIdx.x & 1;
+                const double v = ln ? lb : la;
+                double* dst = L.peer_red[q] + ((size_t) (xs.epoch & 1ull) * MPSB_MAX_RANKS + L.rank) * 4 + ln * 2;
+                asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %2};" ::"l"(dst), "r"((unsigned) __double2loint(v)), "r"(fl),
+                             "r"((unsigned) __double2hiint(v))
+                             : "memory");
+            }
+        } else if ((int) threadIdx.x < W) {
+            st_release_sys(L.peer_flag[threadIdx.x] + L.rank, xs.epoch);
         }
     }
-    if ((int) threadIdx.x < W) {
-        const unsigned long long t0 = global_timer_ns();
-        while (ld_acquire_sys(L.flag + threadIdx.x) < xs.epoch) {
-            if (global_timer_ns() - t0 > 20000000000ull) { // 20 s: a peer is gone
-                atomicOr(&P.stats->error_flags, 8);
-                __threadfence_system();
-                __trap();
+    if (MODE != XCHG_PUBLISH) {
+        if ((int) threadIdx.x < 2 * W) {
+            const int q = threadIdx.x >> 1, ln = threadIdx.x & 1;
+            const double* src = L.red + ((size_t) (xs.epoch & 1ull) * MPSB_MAX_RANKS + q) * 4 + ln * 2;
+            const unsigned long long t0 = global_timer_ns();
+            unsigned x, f0, y, f1, spins = 0;
+            for (;;) {
+                asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(x), "=r"(f0), "=r"(y), "=r"(f1) : "l"(src) : "memory");
+                if (f0 == fl && f1 == fl) break;
+                if ((++spins & 1023u) == 0) xchg_timeout(P, t0);
             }
+            xr[q][ln] = __hiloint2double((int) y, (int) x);
+            __threadfence(); // acquire side: what this rank's CTAs wrote before arriving is visible after the barrier below
         }
+    } else if ((int) threadIdx.x < W) {
+        const unsigned long long t0 = global_timer_ns();
+        unsigned spins = 0;
+        while (ld_acquire_sys(L.flag + threadIdx.x) < xs.epoch)
+            if ((++spins & 1023u) == 0) xchg_timeout(P, t0);
     }
     __syncthreads();
 }
-__device__ __forceinline__ double xchg_slot(const Params& P, const Xchg& xs, int q, int k) {
-    return __ldcg(P.L.red + ((size_t) (xs.epoch & 1ull) * MPSB_MAX_RANKS + q) * 4 + k);
-}
 // sum over ranks in rank order: bit-identical on every rank
-__device__ __forceinline__ void xchg_sum2(const Params& P, const Xchg& xs, double& a, double& b) {
+__device__ __forceinline__ void xchg_sum2(const Params& P, double (*xr)[2], double& a, double& b) {
     a = 0.0;
     b = 0.0;
     for (int q = 0; q < P.L.world; q++) {
-        a += xchg_slot(P, xs, q, 0);
-        b += xchg_slot(P, xs, q, 1);
+        a += xr[q][0];
+        b += xr[q][1];
     }
 }
 
@@ -514,10 +538,10 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
             cmn = fmin(cmn, (double) P.ell_cmin[sl]);
             cmx = fmax(cmx, (double) P.ell_cmax[sl]);
         }
-        xchg_all<true>(P, xs, cmn, cmx, part0, part1, sh, &sm.flag);
+        xchg_all<XCHG_MINMAX>(P, xs, cmn, cmx, part0, part1, sh, &sm.flag, sm.xr);
         if ((int) threadIdx.x < W) {
             const int q = threadIdx.x;
-            double a = xchg_slot(P, xs, q, 0), b = xchg_slot(P, xs, q, 1);
+            double a = sm.xr[q][0], b = sm.xr[q][1];
             int lo = 0, hi = 0; // empty: a rank without active rows needs nothing
             if (a <= b && q != rank) {
                 lo = max((int) a, row_lo);
@@ -539,11 +563,12 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
             double* dst = P.L.peer_p[q];
             for (int i = sm.need[q][0] + tid; i < sm.need[q][1]; i += stride) dst[i] = p[i];
         }
+        xchg_all<XCHG_PUBLISH>(P, xs, 0.0, 0.0, part0, part1, sh, &sm.flag, sm.xr); // the halo rows are visible before any sweep A
     }
     double rhsNorm2, absNew;
     if (MULTI) {
-        xchg_all<false>(P, xs, l0, l1, part0, part1, sh, &sm.flag);
-        xchg_sum2(P, xs, rhsNorm2, absNew);
+        xchg_all<XCHG_SUM>(P, xs, l0, l1, part0, part1, sh, &sm.flag, sm.xr);
+        xchg_sum2(P, sm.xr, rhsNorm2, absNew);
     } else {
         block_sum2(l0, l1, sh);
         if (threadIdx.x == 0) {
@@ -575,6 +600,8 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
             if (i >= sm.need[q][0] && i < sm.need[q][1]) P.L.peer_p[q][i] = v;
     };
 
+    // pairs of active rows at the high end of the block that some peer reads (sweep C handles them first)
+    const int high_pairs = MULTI ? max(0, min(pair_hi - pair_lo, pair_hi - (max(push_gap_hi, row_lo) >> 1))) : 0;
     long long cyc[4] = {0, 0, 0, 0}, t0 = clock64(), t1;
 #define PCG_TICK(slot) do { t1 = clock64(); cyc[slot] += t1 - t0; t0 = t1; } while (0)
     while (!done && it < maxIters) {
@@ -595,8 +622,8 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
         }
         double pap, unused;
         if (MULTI) {
-            xchg_all<false>(P, xs, lpap, dummy, part0, part1, sh, &sm.flag);
-            xchg_sum2(P, xs, pap, unused);
+            xchg_all<XCHG_SUM>(P, xs, lpap, dummy, part0, part1, sh, &sm.flag, sm.xr);
+            xchg_sum2(P, sm.xr, pap, unused);
         } else {
             block_sum2(lpap, dummy, sh);
             if (threadIdx.x == 0) part0[blockIdx.x] = lpap;
@@ -630,8 +657,8 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
         PCG_TICK(1);
         double rz;
         if (MULTI) {
-            xchg_all<false>(P, xs, lrr, lrz, part1, part2, sh, &sm.flag);
-            xchg_sum2(P, xs, residualNorm2, rz);
+            xchg_all<XCHG_SUM>(P, xs, lrr, lrz, part1, part2, sh, &sm.flag, sm.xr);
+            xchg_sum2(P, sm.xr, residualNorm2, rz);
         } else {
             block_sum2(lrr, lrz, sh);
             if (threadIdx.x == 0) {
@@ -644,10 +671,13 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
         if (residualNorm2 < threshold) break;
         const double beta = rz / absNew;
         absNew = rz;
-        PCG_TICK(3);
+        PCG_TICK(PCG_SPLIT_SYNC ? 1 : 3);
         // ---- sweep C: p = z + beta p (MULTI: halo rows also go to the peers that read them) ----
+        // MULTI: the rows peers read above this block (the high end) go first, then the block from its low end,
+        // so every remote store is issued early and its acknowledgement is back before the publishing fence
 #pragma unroll 2
-        for (int i = pair_lo + tid; i < pair_hi; i += stride) {
+        for (int j = tid; j < pair_hi - pair_lo; j += stride) {
+            const int i = MULTI ? (j < high_pairs ? pair_hi - high_pairs + j : pair_lo + j - high_pairs) : pair_lo + j;
             double2 pp = reinterpret_cast<const double2*>(p)[i], rr = reinterpret_cast<const double2*>(r)[i];
             double2 dd = reinterpret_cast<const double2*>(invd)[i];
             pp.x = dd.x * rr.x + beta * pp.x;
@@ -666,9 +696,9 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
         }
         it++;
         PCG_TICK(2);
-        if (MULTI) xchg_all<false>(P, xs, 0.0, 0.0, part0, part1, sh, &sm.flag); // barrier + publishes the halo rows
+        if (MULTI) xchg_all<XCHG_PUBLISH>(P, xs, 0.0, 0.0, part0, part1, sh, &sm.flag, sm.xr); // barrier + publishes the halo rows
         else grid.sync();
-        PCG_TICK(3);
+        PCG_TICK(PCG_SPLIT_SYNC ? 2 : 3);
     }
     if (threadIdx.x == 0) { // per-CTA diagnostic rows behind the three reduction rows
         long long* dbg = reinterpret_cast<long long*>(P.cg_partials + 3 * (size_t) max_blocks);
