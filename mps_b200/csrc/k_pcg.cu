@@ -710,6 +710,7 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
     if (tid == 0) {
         for (int k = 0; k < 4; k++) P.stats->cg_cycles[k] = cyc[k];
         P.stats->cg_iterations   = it;
+        P.stats->pad[0]          = col16 ? 1 : 0;
         P.stats->rhs_norm2       = rhsNorm2;
         P.stats->cg_rel_residual = rhsNorm2 > 0.0 ? sqrt(residualNorm2 / rhsNorm2) : 0.0;
         if (MULTI) *P.L.epoch = xs.epoch; // every CTA read the old value before its first exchange

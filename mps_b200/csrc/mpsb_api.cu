@@ -91,6 +91,7 @@ void fill_stats(mpsb_handle* h, mpsb_step_stats* st) {
     st->n_unconnected   = d.n_unconnected;
     st->n_collisions    = d.n_collisions;
     st->max_neighbors   = d.max_neighbors;
+    st->ppe_columns_16bit = d.pad[0];
     st->courant_exceeds_cfl = d.courant_bits_as_double > h->P.s.cfl_condition;
 }
 

@@ -32,7 +32,7 @@ struct DevStats {
     int n_collisions;
     int max_neighbors;
     int error_flags; // bit0 capacity, bit1 out-of-grid, bit2 event overflow
-    int pad[2];
+    int pad[2]; // pad[0]: the last solve streamed 16-bit column offsets
     long long cg_cycles[4]; // CTA 0's SM cycles in sweep A / B / C / reductions+grid barriers (diagnostic)
 };
 
