@@ -59,22 +59,38 @@ __global__ void radix_hist_kernel(const unsigned* __restrict__ key, int n, int s
     hist[threadIdx.x * numTiles + blockIdx.x] = sh[threadIdx.x];
 }
 
-// Exclusive scan of a moderate-size int array by one CTA (running carry over 4096-element chunks).
-__global__ void exclusive_scan_kernel(int* __restrict__ data, int n) {
-    constexpr int T = 1024, IT = 4;
+// Exclusive scan of a moderate-size int array by one CTA: a running carry over chunks of 16 384 elements,
+// 16 consecutive elements per thread loaded as four int4 (the array base is 256-byte aligned and every
+// chunk starts at a multiple of 16), the next chunk's loads issued before the current chunk's barriers.
+__global__ void __launch_bounds__(1024) exclusive_scan_kernel(int* __restrict__ data, int n) {
+    constexpr int T = 1024, IT = 16;
     __shared__ int warp_sums[32];
     __shared__ int carry_sh;
     if (threadIdx.x == 0) carry_sh = 0;
     __syncthreads();
-    int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (int base = 0; base < n; base += T * IT) {
-        int idx = base + threadIdx.x * IT;
-        int v[IT], sum = 0;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    auto load = [&](int base, int (&v)[IT]) {
+        const int idx = base + threadIdx.x * IT;
+        if (idx + IT <= n) {
 #pragma unroll
-        for (int k = 0; k < IT; k++) {
-            v[k] = (idx + k < n) ? data[idx + k] : 0;
-            sum += v[k];
+            for (int q = 0; q < IT / 4; q++) {
+                int4 t = reinterpret_cast<const int4*>(data + idx)[q];
+                v[4 * q] = t.x; v[4 * q + 1] = t.y; v[4 * q + 2] = t.z; v[4 * q + 3] = t.w;
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < IT; k++) v[k] = (idx + k < n) ? data[idx + k] : 0;
         }
+    };
+    int cur[IT], nxt[IT];
+    load(0, cur);
+    for (int base = 0; base < n; base += T * IT) {
+        const bool more = base + T * IT < n;
+        if (more) load(base + T * IT, nxt);
+        const int idx = base + threadIdx.x * IT;
+        int sum = 0;
+#pragma unroll
+        for (int k = 0; k < IT; k++) sum += cur[k];
         int incl = sum;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -93,16 +109,31 @@ __global__ void exclusive_scan_kernel(int* __restrict__ data, int n) {
             warp_sums[lane] = wi - ws; // exclusive warp offsets
         }
         __syncthreads();
-        int carry = carry_sh;
-        int excl  = carry + warp_sums[warp] + (incl - sum);
+        int excl = carry_sh + warp_sums[warp] + (incl - sum);
+        if (idx + IT <= n) {
 #pragma unroll
-        for (int k = 0; k < IT; k++) {
-            if (idx + k < n) data[idx + k] = excl;
-            excl += v[k];
+            for (int q = 0; q < IT / 4; q++) {
+                int4 t;
+                t.x = excl; excl += cur[4 * q];
+                t.y = excl; excl += cur[4 * q + 1];
+                t.z = excl; excl += cur[4 * q + 2];
+                t.w = excl; excl += cur[4 * q + 3];
+                reinterpret_cast<int4*>(data + idx)[q] = t;
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < IT; k++) {
+                if (idx + k < n) data[idx + k] = excl;
+                excl += cur[k];
+            }
         }
         __syncthreads();
         if (threadIdx.x == T - 1) carry_sh = excl; // last thread holds the chunk total + carry
         __syncthreads();
+        if (more) {
+#pragma unroll
+            for (int k = 0; k < IT; k++) cur[k] = nxt[k];
+        }
     }
 }
 

@@ -20,6 +20,7 @@ __global__ void __launch_bounds__(128) neighbor_kernel(Params P) {
     }
     const double xi = P.S.x[s], yi = P.S.y[s], zi = P.S.z[s];
     const double re = P.s.re_max;
+    const double re2_out = (re * re) * (1.0 + 0x1p-50); // >= re^2 in exact arithmetic (the product errs by < 2^-53 relative)
     unsigned key = P.key[s];
     int nxy = P.numX * P.numY;
     int iz = key / nxy, rem = key - iz * nxy;
@@ -35,7 +36,12 @@ __global__ void __launch_bounds__(128) neighbor_kernel(Params P) {
                 int b = P.cell_start[c], e = P.cell_end[c];
                 for (int j = b; j < e; j++) {
                     double dx = P.S.x[j] - xi, dy = P.S.y[j] - yi, dz = P.S.z[j] - zi;
-                    double dist = sqrt((dx * dx + dy * dy) + dz * dz); // Eigen (pj - pi).norm()
+                    double d2 = (dx * dx + dy * dy) + dz * dz;
+                    // 70 % of the candidates of a 3x3(x3) cell block are out of range: skip their square root.
+                    // d2 >= re2_out implies sqrt(d2) >= re exactly, hence RN(sqrt(d2)) >= re: the reference's
+                    // `dist < re` is false for them whatever the rounding, so the kept set is unchanged.
+                    if (d2 >= re2_out) continue;
+                    double dist = sqrt(d2); // Eigen (pj - pi).norm()
                     if (j != s && dist < re) {
                         if (count < P.K) {
                             P.nbr_idx[SELL(count, s)]  = j;
