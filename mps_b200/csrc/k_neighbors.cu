@@ -26,11 +26,18 @@ __global__ void __launch_bounds__(128) neighbor_kernel(Params P) {
     int iz = key / nxy, rem = key - iz * nxy;
     int iy = rem / P.numX, ix = rem - iy * P.numX;
     int count = 0;
+    // A domain of zero thickness in z (every 2-D case) keeps all non-ghost particles at z == zmin, i.e. in the
+    // plane iz == 1 (anything else is out of the domain and a ghost): the planes iz +- 1 are empty, skip them.
+    const int zspan = P.s.domain_max[2] == P.s.domain_min[2] ? 0 : 1;
+    // not unrolled: 27 copies of the inner loop (with its inlined fp64 square root) overflow the instruction cache
+#pragma unroll 1
     for (int jx = ix - 1; jx <= ix + 1; jx++) {
         if (jx < 0 || jx >= P.numX) continue;
+#pragma unroll 1
         for (int jy = iy - 1; jy <= iy + 1; jy++) {
             if (jy < 0 || jy >= P.numY) continue;
-            for (int jz = iz - 1; jz <= iz + 1; jz++) {
+#pragma unroll 1
+            for (int jz = iz - zspan; jz <= iz + zspan; jz++) {
                 if (jz < 0 || jz >= P.numZ) continue;
                 int c = jx + jy * P.numX + jz * nxy;
                 int b = P.cell_start[c], e = P.cell_end[c];
