@@ -278,7 +278,9 @@ def case_paths(name: str):
 
 
 def load_case(name: str):
-    """(Settings, type, pos, vel) of a shipped case under cases/<name>/."""
+    """(Settings, type, pos, vel) of a shipped case under cases/<name>/ (or the generated 3-D case "tank3d")."""
+    if name == "tank3d":
+        return tank3d(jitter=0.05)
     yml, _ = case_paths(name)
     s = load_settings(yml)
     csv = s.input_csv_path if os.path.isabs(s.input_csv_path) else os.path.join(REPO_ROOT, s.input_csv_path)
@@ -364,3 +366,41 @@ def write_settings_yaml(s: Settings, path: str, finish_time=None, output_interva
     with open(path, "w") as f:
         f.write("\n".join(lines) + "\n")
     return path
+
+
+def tank3d(n_fluid=(8, 10, 6), n_tank=(16, 14, 6), l0=0.01, ratio=2.1, jitter=0.0):
+    """Synthetic 3-D case (the reference ships none): an open-top tank of n_tank lattice cells
+    with one wall layer and two dummy-wall layers on the bottom and the four sides, a fluid column of
+    n_fluid cells in the corner x = z = 0, dambreak's physical settings with dim = 3 and radius ratio `ratio`.
+    ids dense in loop order x outer, y, z inner (the reference generators' convention extended by one axis).
+    `jitter` > 0 displaces fluid particles by a fixed pseudo-random pattern (mt19937 seed 1, +-jitter*l0) so
+    that neighbour distances are not lattice-degenerate."""
+    s = load_settings(case_paths("dambreak")[0])
+    s.dim = 3
+    s.particle_distance = l0
+    s.dt = 0.1 * l0
+    s.re_pressure = s.re_viscosity = s.re_surface = s.re_max = ratio * l0
+    s.collision_distance = 0.5 * l0
+    X, Y, Z = (n * l0 for n in n_tank)
+    s.domain_min = (-0.1, -0.1, -0.1)
+    s.domain_max = (X + 0.1, Y + 0.1, Z + 0.1)
+    s.input_csv_path = ""
+    a = 3
+    ix = np.arange(-a, n_tank[0] + a)
+    iy = np.arange(-a, n_tank[1])
+    iz = np.arange(-a, n_tank[2] + a)
+    gx, gy, gz = np.meshgrid(ix, iy, iz, indexing="ij")
+    inside = lambda lo: (gx >= -lo) & (gx < n_tank[0] + lo) & (gy >= -lo) & (gz >= -lo) & (gz < n_tank[2] + lo)  # noqa: E731
+    t = np.full(gx.shape, GHOST, dtype=np.int32)
+    t[inside(3)] = DUMMY_WALL
+    t[inside(1)] = WALL
+    t[inside(0)] = GHOST
+    t[(gx >= 0) & (gx < n_fluid[0]) & (gy >= 0) & (gy < n_fluid[1]) & (gz >= 0) & (gz < n_fluid[2])] = FLUID
+    keep = (t != GHOST).ravel()
+    pos = np.stack([(g.ravel()[keep] + 0.5) * l0 for g in (gx, gy, gz)], axis=1)
+    types = np.ascontiguousarray(t.ravel()[keep])
+    if jitter > 0.0:
+        rng = np.random.Generator(np.random.MT19937(1))
+        d = rng.uniform(-jitter * l0, jitter * l0, size=pos.shape)
+        pos[types == FLUID] += d[types == FLUID]
+    return s, types, np.ascontiguousarray(pos), np.zeros_like(pos)

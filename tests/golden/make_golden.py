@@ -24,6 +24,7 @@ PLAN = {
     "dambreak_fine": [0, 60],
     "dambreak_fine_original": [0, 20],
     "dambreak_fine_higher_order": [0, 20],
+    "tank3d": [0, 5],                              # generated 3-D case (mps_b200.cases.tank3d); the reference ships none
 }
 
 
@@ -34,10 +35,20 @@ def nb_digest(start, ids, dist):
 
 
 def main():
+    only = sys.argv[1:]  # optional: regenerate only these cases
     for case, steps in PLAN.items():
-        yml, _ = C.case_paths(case)
-        S = C.load_settings(yml)
-        ref = R.RefMPS(yml, os.path.join(ROOT, S.input_csv_path))
+        if only and case not in only:
+            continue
+        if case == "tank3d":
+            import tempfile
+
+            S, t, p, v = C.load_case(case)
+            yml = C.write_settings_yaml(S, os.path.join(tempfile.mkdtemp(prefix="mpsb_golden_"), "settings.yml"))
+            ref = R.RefMPS(yml, arrays=(t, p, v))
+        else:
+            yml, _ = C.case_paths(case)
+            S = C.load_settings(yml)
+            ref = R.RefMPS(yml, os.path.join(ROOT, S.input_csv_path))
         k = 0
         for target in steps:
             while k < target:

@@ -91,7 +91,7 @@ def test_phases_teacher_forced(path):
 def test_step_teacher_forced(path):
     """One whole mpsb_step from the reference's state against the reference's own next state."""
     z, before, after = U.load_golden(path)
-    S = C.load_settings(C.case_paths(U.golden_case(path))[0])
+    S = C.load_case(U.golden_case(path))[0]
     dev = capi.DeviceMPS(S, before["type"], before["position"], before["velocity"])
     dev.upload(before)
     courant = dev.step_forward(bool(z["export"]))

@@ -42,11 +42,15 @@ def test_oracle_ppe_and_cg_match_golden(path):
 
 
 @pytest.mark.skipif(not R.have_ref(), reason="oracle/_ref not built (needs /root/reference)")
-@pytest.mark.parametrize("case,steps", [("dambreak", 120), ("hydrostatic", 6), ("dambreak_fine_higher_order", 4)])
-def test_oracle_free_run_matches_compiled_reference(case, steps):
-    yml, _ = C.case_paths(case)
+@pytest.mark.parametrize("case,steps", [("dambreak", 120), ("hydrostatic", 6), ("dambreak_fine_higher_order", 4),
+                                        ("tank3d", 6)])
+def test_oracle_free_run_matches_compiled_reference(case, steps, tmp_path):
     S, t, p, v = C.load_case(case)
-    ref = R.RefMPS(yml, S.input_csv_path if S.input_csv_path.startswith("/") else U.ROOT + "/" + S.input_csv_path)
+    if case == "tank3d":  # generated 3-D case: the reference takes its settings from a YAML written for it
+        ref = R.RefMPS(C.write_settings_yaml(S, str(tmp_path / "settings.yml")), arrays=(t, p, v))
+    else:
+        yml, _ = C.case_paths(case)
+        ref = R.RefMPS(yml, S.input_csv_path if S.input_csv_path.startswith("/") else U.ROOT + "/" + S.input_csv_path)
     orc = R.OracleMPS(S.to_c(), t, p, v)
     for k in range(steps):
         exp = k % 7 == 0
