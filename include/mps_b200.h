@@ -86,7 +86,7 @@ typedef struct mpsb_step_stats {
     int32_t max_neighbors;   /* longest neighbour list seen in the step */
     int32_t courant_exceeds_cfl; /* 1 if courant > cfl_condition (debugLogCount += ) */
     int32_t ppe_columns_16bit;   /* 1: the solve streamed 16-bit column offsets (10 B per entry), 0: int32 columns (12 B) */
-    int32_t reserved;
+    int32_t solve_in_cluster;    /* 1: the small-system cluster kernel did the solve (k_pcg_cluster.cu), 0: the grid kernel */
 } mpsb_step_stats;
 
 typedef struct mpsb_handle mpsb_handle;

@@ -38,11 +38,11 @@ class CStepStats(ct.Structure):
         ("ms_assemble", ct.c_double), ("ms_solve", ct.c_double), ("ms_correct", ct.c_double),
         ("cg_iterations", ct.c_int32), ("n_active", ct.c_int32), ("n_inner", ct.c_int32), ("n_surface", ct.c_int32),
         ("nnz", ct.c_int32), ("n_ghosted", ct.c_int32), ("n_unconnected", ct.c_int32), ("n_collisions", ct.c_int32),
-        ("max_neighbors", ct.c_int32), ("courant_exceeds_cfl", ct.c_int32), ("ppe_columns_16bit", ct.c_int32), ("reserved", ct.c_int32),
+        ("max_neighbors", ct.c_int32), ("courant_exceeds_cfl", ct.c_int32), ("ppe_columns_16bit", ct.c_int32), ("solve_in_cluster", ct.c_int32),
     ]
 
     def as_dict(self):
-        return {n: getattr(self, n) for n, _ in self._fields_ if n != "reserved"}
+        return {n: getattr(self, n) for n, _ in self._fields_}
 
 
 class CFields(ct.Structure):

@@ -478,6 +478,8 @@ bulk_g2s(S.val, P.ell_val + off, (unsigned) nsl * 256u, bar);
 // MULTI = false: one GPU, rows [0, n). MULTI = true: this rank's row block; see the file header.
 template <bool MULTI>
 __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_blocks, int iteration_cap) {
+    if (*P.cluster_done) return; // the cluster solve (k_pcg_cluster.cu) already did it; uniform over the grid
+    if (blockIdx.x == 0 && threadIdx.x == 0) P.stats->t_solve_begin = global_timer_ns();
     cg::grid_group grid = cg::this_grid();
     extern __shared__ __align__(128) unsigned char smem_raw[];
     Smem& sm = *reinterpret_cast<Smem*>(smem_raw);
@@ -711,6 +713,8 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
         for (int k = 0; k < 4; k++) P.stats->cg_cycles[k] = cyc[k];
         P.stats->cg_iterations   = it;
         P.stats->pad[0]          = col16 ? 1 : 0;
+        P.stats->pad[1]          = 0;
+        P.stats->t_solve_end     = global_timer_ns();
         P.stats->rhs_norm2       = rhsNorm2;
         P.stats->cg_rel_residual = rhsNorm2 > 0.0 ? sqrt(residualNorm2 / rhsNorm2) : 0.0;
         if (MULTI) *P.L.epoch = xs.epoch; // every CTA read the old value before its first exchange
@@ -737,6 +741,7 @@ int mpsb_pcg_configure(mpsb_handle* h) {
 void mpsb_launch_pcg(mpsb_handle* h) {
     Params& P = h->P;
     const bool multi = P.L.world > 1;
+    mpsb_launch_pcg_cluster(h); // small systems: one cluster, problem resident in shared memory; sets *cluster_done
     // one 32-row slice per warp at least; never more CTAs than can be co-resident (cooperative launch)
     int want = mpsb_div_up(P.Np / 32 / (multi ? P.L.world : 1), PCG_WARPS);
     int grid = want < h->cg_max_blocks ? want : h->cg_max_blocks;

@@ -92,6 +92,7 @@ void fill_stats(mpsb_handle* h, mpsb_step_stats* st) {
     st->n_collisions    = d.n_collisions;
     st->max_neighbors   = d.max_neighbors;
     st->ppe_columns_16bit = d.pad[0];
+    st->solve_in_cluster  = d.pad[1];
     st->courant_exceeds_cfl = d.courant_bits_as_double > h->P.s.cfl_condition;
 }
 
@@ -205,6 +206,15 @@ int mpsb_create(const mpsb_settings* settings, int64_t n, const int32_t* type, c
     }
     CKC(dalloc(&P.cg_partials, 8 * (size_t) h->cg_max_blocks + 8));
     CKC(dalloc(&P.cg_slice_pap, N / 32 + 1));
+    CKC(dalloc(&P.cluster_done, 1));
+    mpsb_pcg_cluster_configure(h); // optional fast path for small systems; 0 = this device cannot co-schedule a cluster
+    {
+        const char* nc = getenv("MPSB_NO_CLUSTER_SOLVE");
+        h->cl_disable  = nc && atoi(nc) ? 1 : 0;
+        const char* ng = getenv("MPSB_NO_STEP_GRAPH");
+        h->graph_enable = ng && atoi(ng) ? 0 : 1;
+        h->n_graphs     = 0;
+    }
     // initial state: type/position/velocity from the caller, everything else 0 / Ignored (SURVEY B-1)
     CKC(cudaMemcpy(H.type, type, sizeof(int) * (size_t) n, cudaMemcpyHostToDevice));
     CKC(cudaMemcpy(H.pos, position, sizeof(double) * 3 * (size_t) n, cudaMemcpyHostToDevice));
@@ -222,13 +232,16 @@ int mpsb_destroy(mpsb_handle* h) {
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     mpsb_comm_release(h);
+    for (int k = 0; k < h->n_graphs; k++)
+        if (h->graphs[k].exec) cudaGraphExecDestroy(h->graphs[k].exec);
+    h->n_graphs = 0;
     Params& P = h->P;
     Sorted& S = P.S;
     Home& H   = P.H;
     void* ptrs[] = {S.x, S.y, S.z, S.u, S.v, S.w, S.u2, S.v2, S.w2, S.ax, S.ay, S.az, S.p, S.minp, S.ratio, S.type,
                     S.bc, S.id, H.pos, H.vel, H.acc, H.p, H.minp, H.ratio, H.type, H.bc, H.inv, P.key, P.key_alt,
                     P.val, P.val_alt, P.cell_start, P.cell_end, P.nbr_count, P.nbr_idx, P.nbr_dist, P.ell_count,
-                    P.ell_width, P.ell_cmin, P.ell_cmax, P.ell_col, P.ell_col16, P.ell_wide, P.ell_val, P.diag, P.rhs, P.cg_r, P.cg_p, P.cg_ap, P.cg_invdiag, P.cg_partials, P.cg_slice_pap,
+                    P.ell_width, P.ell_cmin, P.ell_cmax, P.ell_col, P.ell_col16, P.ell_wide, P.ell_val, P.diag, P.rhs, P.cg_r, P.cg_p, P.cg_ap, P.cg_invdiag, P.cg_partials, P.cg_slice_pap, P.cluster_done,
                     P.parent, P.mark, P.cand, P.cand_count, P.ev_ghost_id, P.ev_ghost_xyz, P.ev_uncon_id, P.stats,
                     h->block_hist};
     for (void* p : ptrs)
@@ -299,6 +312,103 @@ int mpsb_download(mpsb_handle* h, uint32_t mask, const mpsb_fields* f) {
     return MPSB_OK;
 }
 
+// The launch sequence of one step on h->stream. `timed`: bracket the phases with CUDA events (direct issue);
+// inside a stream capture only the kernels and memsets are recorded.
+static int issue_step(mpsb_handle* h, int want_number_density, bool timed) {
+    cudaStream_t st = h->stream;
+    cudaEvent_t* E  = h->ev;
+#define EV(k)                                                                                     \
+    do {                                                                                          \
+        if (timed) CK(h, cudaEventRecord(E[k], st));                                              \
+    } while (0)
+    CK(h, cudaMemsetAsync(h->P.stats, 0, sizeof(DevStats), st));
+    EV(0);
+    build_lists(h);                                  // setNeighbors
+    EV(1);
+    mpsb_launch_explicit(h);                         // calcGravity, calcViscosity, moveParticles
+    EV(2);
+    mpsb_launch_scatter_all(h);
+    build_lists(h);                                  // setNeighbors
+    EV(3);
+    mpsb_launch_collision(h);                        // collision
+    EV(4);
+    mpsb_launch_scatter_all(h);
+    build_lists(h);                                  // setNeighbors
+    EV(5);
+    mpsb_launch_flags_source(h);                     // calcPressure ...
+    mpsb_launch_matrix(h);
+    mpsb_launch_dirichlet(h);
+    EV(6);
+    mpsb_launch_pcg(h);
+    if (h->world > 1 && mpsb_comm_gather_pressure(h)) return h->sticky;
+    EV(7);
+    mpsb_launch_pressure_post(h);
+    mpsb_launch_gradient_move(h);                    // calcPressureGradient, moveParticlesWithPressureGradient
+    EV(8);
+    if (want_number_density) {                       // setNumberDensity (:125-127)
+        mpsb_launch_scatter_all(h);
+        build_lists(h);
+        mpsb_launch_number_density(h);
+    }
+    EV(9);
+    mpsb_launch_courant(h);                          // getCourantNumber
+    mpsb_launch_scatter_all(h);
+    EV(10);
+#undef EV
+    return MPSB_OK;
+}
+
+// Small cases are launch-bound (about 57 launches of a few microseconds each): the whole step is captured
+// once per distinct pointer state (the velocity double buffer and the sort buffers swap inside a step) and
+// replayed as ONE CUDA graph launch. Returns 1 if the step was issued through a graph, 0 if the caller must
+// issue it directly, < 0 on a sticky error.
+static int step_through_graph(mpsb_handle* h, int want) {
+    if (!h->graph_enable || h->P.N > 32767 || h->world > 1) return 0;
+    StepGraph* g = nullptr;
+    for (int k = 0; k < h->n_graphs; k++)
+        if (h->graphs[k].u == h->P.S.u && h->graphs[k].key == h->P.key && h->graphs[k].want == want) g = &h->graphs[k];
+    if (!g) {
+        if (h->n_graphs == MPSB_MAX_STEP_GRAPHS) return 0;
+        const Params before = h->P;
+        const int64_t launches0 = h->launches;
+        cudaGraph_t graph = nullptr;
+        if (cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
+            cudaGetLastError();
+            h->graph_enable = 0;
+            return 0;
+        }
+        int rc = issue_step(h, want, false);
+        cudaError_t e = cudaStreamEndCapture(h->stream, &graph);
+        cudaGraphExec_t exec = nullptr;
+        if (rc == MPSB_OK && e == cudaSuccess && graph) e = cudaGraphInstantiate(&exec, graph, 0);
+        if (graph) cudaGraphDestroy(graph);
+        if (rc != MPSB_OK || e != cudaSuccess || !exec) { // not capturable here: issue directly from now on
+            cudaGetLastError();
+            h->sticky       = 0;
+            h->P            = before;
+            h->launches     = launches0;
+            h->graph_enable = 0;
+            return 0;
+        }
+        g           = &h->graphs[h->n_graphs++];
+        g->u        = before.S.u;
+        g->key      = before.key;
+        g->want     = want;
+        g->exec     = exec;
+        g->after    = h->P;
+        g->launches = h->launches - launches0;
+        h->P        = before;
+        h->launches = launches0;
+    }
+    CK(h, cudaEventRecord(h->ev[0], h->stream));
+    CK(h, cudaGraphLaunch(g->exec, h->stream));
+    CK(h, cudaEventRecord(h->ev[10], h->stream));
+    h->P = g->after;
+    h->launches += g->launches;
+    h->have_lists = true;
+    return 1;
+}
+
 // MPS::stepForward (src/mps.cpp:111-130). HOME is current on entry and on exit.
 int mpsb_step(mpsb_handle* h, int want_number_density, mpsb_step_stats* stats) {
     if (!h) return MPSB_ERR_ARG;
@@ -306,41 +416,13 @@ int mpsb_step(mpsb_handle* h, int want_number_density, mpsb_step_stats* stats) {
     if (stats) memset(stats, 0, sizeof *stats);
     if (h->P.N == 0) return MPSB_OK;
     CK(h, cudaSetDevice(h->device));
-    cudaStream_t st = h->stream;
-    cudaEvent_t* E  = h->ev;
-    CK(h, cudaMemsetAsync(h->P.stats, 0, sizeof(DevStats), st));
-    CK(h, cudaEventRecord(E[0], st));
-    build_lists(h);                                  // setNeighbors
-    CK(h, cudaEventRecord(E[1], st));
-    mpsb_launch_explicit(h);                         // calcGravity, calcViscosity, moveParticles
-    CK(h, cudaEventRecord(E[2], st));
-    mpsb_launch_scatter_all(h);
-    build_lists(h);                                  // setNeighbors
-    CK(h, cudaEventRecord(E[3], st));
-    mpsb_launch_collision(h);                        // collision
-    CK(h, cudaEventRecord(E[4], st));
-    mpsb_launch_scatter_all(h);
-    build_lists(h);                                  // setNeighbors
-    CK(h, cudaEventRecord(E[5], st));
-    mpsb_launch_flags_source(h);                     // calcPressure ...
-    mpsb_launch_matrix(h);
-    mpsb_launch_dirichlet(h);
-    CK(h, cudaEventRecord(E[6], st));
-    mpsb_launch_pcg(h);
-    if (h->world > 1 && mpsb_comm_gather_pressure(h)) return h->sticky;
-    CK(h, cudaEventRecord(E[7], st));
-    mpsb_launch_pressure_post(h);
-    mpsb_launch_gradient_move(h);                    // calcPressureGradient, moveParticlesWithPressureGradient
-    CK(h, cudaEventRecord(E[8], st));
-    if (want_number_density) {                       // setNumberDensity (:125-127)
-        mpsb_launch_scatter_all(h);
-        build_lists(h);
-        mpsb_launch_number_density(h);
+    cudaEvent_t* E = h->ev;
+    const int graphed = step_through_graph(h, want_number_density ? 1 : 0);
+    if (graphed < 0) return h->sticky;
+    if (!graphed) {
+        int rc0 = issue_step(h, want_number_density, true);
+        if (rc0) return rc0;
     }
-    CK(h, cudaEventRecord(E[9], st));
-    mpsb_launch_courant(h);                          // getCourantNumber
-    mpsb_launch_scatter_all(h);
-    CK(h, cudaEventRecord(E[10], st));
     int rc = fetch_stats(h);
     if (rc) return rc;
     fill_stats(h, stats);
@@ -350,13 +432,18 @@ int mpsb_step(mpsb_handle* h, int want_number_density, mpsb_step_stats* stats) {
             cudaEventElapsedTime(&t, E[a], E[b]);
             return (double) t;
         };
-        stats->ms_neighbors = ms(0, 1) + ms(2, 3) + ms(4, 5) + ms(8, 9);
-        stats->ms_explicit  = ms(1, 2);
-        stats->ms_collision = ms(3, 4);
-        stats->ms_assemble  = ms(5, 6);
-        stats->ms_solve     = ms(6, 7);
-        stats->ms_correct   = ms(7, 8) + ms(9, 10);
-        stats->ms_total     = ms(0, 10);
+        if (!graphed) {
+            stats->ms_neighbors = ms(0, 1) + ms(2, 3) + ms(4, 5) + ms(8, 9);
+            stats->ms_explicit  = ms(1, 2);
+            stats->ms_collision = ms(3, 4);
+            stats->ms_assemble  = ms(5, 6);
+            stats->ms_solve     = ms(6, 7);
+            stats->ms_correct   = ms(7, 8) + ms(9, 10);
+        } else { // one graph launch: only the solve is stamped (device clock inside the PCG kernels)
+            const DevStats& d = h->host_stats;
+            stats->ms_solve = d.t_solve_end > d.t_solve_begin ? 1e-6 * (double) (d.t_solve_end - d.t_solve_begin) : 0.0;
+        }
+        stats->ms_total = ms(0, 10);
     }
     return check_flags(h);
 }

@@ -34,6 +34,7 @@ struct DevStats {
     int error_flags; // bit0 capacity, bit1 out-of-grid, bit2 event overflow
     int pad[2]; // pad[0]: the last solve streamed 16-bit column offsets
     long long cg_cycles[4]; // CTA 0's SM cycles in sweep A / B / C / reductions+grid barriers (diagnostic)
+    unsigned long long t_solve_begin, t_solve_end; // %globaltimer (ns) at the start / end of the solve kernel that did the work
 };
 
 // Sorted-order SoA working set (all arrays have N entries).
@@ -115,6 +116,7 @@ struct Params {
     double *cg_r, *cg_p, *cg_ap, *cg_invdiag; // N
     double *cg_partials;       // 8 * max_blocks + 1: 3 reduction rows, 5 diagnostic rows, 2 slice-queue counters
     double *cg_slice_pap;      // Np/32 + 1: p.Ap of each 32-row slice (deterministic two-level sum)
+    int *cluster_done;         // 1     set by the cluster solve (k_pcg_cluster.cu) when it did the solve
     // Dirichlet connectivity
     int *parent;               // N
     int *mark;                 // N
@@ -129,6 +131,17 @@ struct Params {
     PeerLinks L;
 };
 
+// One captured step (mpsb_api.cu): valid for the pointer state it was captured in.
+#define MPSB_MAX_STEP_GRAPHS 8
+struct StepGraph {
+    const void* u;      // P.S.u at capture (velocity double buffer parity)
+    const void* key;    // P.key at capture (sort buffer parity)
+    int want;           // want_number_density
+    cudaGraphExec_t exec;
+    Params after;       // P after the step's pointer swaps
+    int64_t launches;   // kernel launches inside the graph
+};
+
 struct mpsb_handle {
     Params P;
     int device;
@@ -141,6 +154,11 @@ struct mpsb_handle {
     int cg_smem;            // dynamic shared memory of the PCG kernel
     int cg_iteration_cap;   // diagnostic: stop the solve after this many iterations (0 = Eigen's 2N)
     int num_sms;
+    int cl_size, cl_smem;   // cluster solve for small systems (k_pcg_cluster.cu): cluster size (0 = unavailable), dynamic smem
+    int cl_disable;         // MPSB_NO_CLUSTER_SOLVE=1: always use the grid kernel (tests)
+    int graph_enable;       // small cases: replay the step as one CUDA graph (MPSB_NO_STEP_GRAPH=1 disables)
+    int n_graphs;
+    StepGraph graphs[MPSB_MAX_STEP_GRAPHS];
     int64_t launches;
     bool have_lists;        // a neighbour build has happened since the last position upload
     DevStats host_stats;
@@ -168,6 +186,8 @@ void mpsb_launch_dirichlet(mpsb_handle* h);
 void mpsb_launch_pressure_post(mpsb_handle* h);
 void mpsb_launch_pcg(mpsb_handle* h);                   // k_pcg.cu
 int mpsb_pcg_configure(mpsb_handle* h);
+int mpsb_pcg_cluster_configure(mpsb_handle* h);         // k_pcg_cluster.cu
+int mpsb_launch_pcg_cluster(mpsb_handle* h);
 int mpsb_comm_gather_pressure(mpsb_handle* h);          // mpsb_comm.cu: all-gather the solved row blocks of p
 void mpsb_comm_release(mpsb_handle* h);
 

@@ -266,3 +266,63 @@ def test_16_bit_and_32_bit_column_streams_give_identical_solves(monkeypatch):
         dev.close()
     assert np.array_equal(out[0][0], out[1][0]) and out[0][1:] == out[1][1:]
     assert np.abs(out[0][0]).max() > 0
+
+
+OBSERVABLE_RUNS = {  # case -> (x_front tolerance [m], relative p_bottom tolerance); chaos grows with the step count
+    "dambreak": (1e-6, 1e-6),        # north_star / SURVEY §7.3-E: x_front within 1e-6 m for t <= 0.25 s
+    "dambreak_fine": (1e-5, 1e-4),
+    "hydrostatic": (1e-6, 1e-6),
+}
+
+
+@pytest.mark.parametrize("case", list(OBSERVABLE_RUNS))
+def test_free_run_observables_match_reference_series(case):
+    """Free-running GPU simulation against the reference's own free run (tests/golden/observables.json, made by
+    tests/golden/make_observables.py from the compiled reference): dam-break front position and hydrostatic
+    bottom-row mean pressure within the stated tolerance over the run, fluid count identical."""
+    import json
+    import os
+
+    obs = json.load(open(os.path.join(U.GOLDEN, "observables.json")))[case]
+    S, t, p, v = C.load_case(case)
+    dev = capi.DeviceMPS(S, t, p, v)
+    dev.load_initial_state()
+    tol_x, tol_p = OBSERVABLE_RUNS[case]
+    k = 0
+    for mark in sorted(int(m) for m in obs["series"]):
+        while k < mark:
+            dev.step_forward(False)
+            k += 1
+        st = dev.download(["type", "position", "pressure"])
+        want = obs["series"][str(mark)]
+        fluid = st["type"] == C.FLUID
+        assert int(fluid.sum()) == want["n_fluid"], (case, mark)
+        assert abs(float(st["position"][fluid, 0].max()) - want["x_front"]) <= tol_x, (case, mark)
+        assert abs(float(st["position"][fluid, 1].max()) - want["y_top"]) <= tol_x, (case, mark)
+        bottom = fluid & (st["position"][:, 1] < S.particle_distance)
+        if want["p_bottom"] != 0.0:
+            pb = float(st["pressure"][bottom].mean())
+            assert abs(pb - want["p_bottom"]) <= tol_p * abs(want["p_bottom"]), (case, mark, pb, want["p_bottom"])
+    dev.close()
+
+
+@pytest.mark.parametrize("case", ["dambreak", "hydrostatic", "dambreak_fine"])
+def test_cluster_solve_is_used_for_shipped_sizes_and_agrees_with_grid_solve(case, monkeypatch):
+    """Small systems are solved by one thread-block cluster with the problem resident in shared memory
+    (k_pcg_cluster.cu); MPSB_NO_CLUSTER_SOLVE=1 forces the persistent grid kernel. Same method and stopping
+    rule, different reduction order: pressures within 1e-10, iteration counts within 2 %."""
+    S, t, p, v = C.load_case(case)
+    out = []
+    for no_cluster in ("0", "1"):
+        monkeypatch.setenv("MPSB_NO_CLUSTER_SOLVE", no_cluster)
+        dev = capi.DeviceMPS(S, t, p, v)
+        dev.load_initial_state()
+        for name, dph, _ in PHASE_MAP[:8]:
+            dev.run_phase(dph)
+        st = dev.run_phase(capi.PH_SOLVE)
+        out.append((dev.download(["pressure"])["pressure"], st.cg_iterations, st.solve_in_cluster, st.cg_rel_residual))
+        dev.close()
+    assert out[0][2] == 1 and out[1][2] == 0, "cluster kernel not taken / not bypassed"
+    assert U.rel_err(out[0][0], out[1][0]) <= TOL
+    assert abs(out[0][1] - out[1][1]) <= max(2, 0.02 * out[1][1])
+    assert out[0][3] <= 2.3e-16
