@@ -7,11 +7,13 @@
 // L2 (about 4 us) costs more than an iteration's arithmetic. Here
 //   * the cluster's CTAs (8 or 16, one per SM of a GPC) each own a block of 32-row slices and copy their
 //     part of the sliced-ELL matrix (fp64 values, 16-bit column offsets, diagonal) into shared memory ONCE;
-//   * every CTA keeps a full replica of the search direction p; sweep C writes the new rows into all
-//     replicas through distributed shared memory (DSMEM);
-//   * reductions are CTA partials stored into every CTA's shared memory and summed in rank order (every CTA
-//     gets bit-identical scalars); the only synchronisation is the hardware cluster barrier, three per
-//     iteration.
+//   * every CTA keeps a WINDOW of the search direction p — its own rows plus the rows its block's columns
+//     reach (one cell row either side in the cell-major order) — and a window of z = D^-1 r; sweep B stores
+//     each new z row into every window that holds it through distributed shared memory (DSMEM), and
+//     p = z + beta p is then formed locally on the whole window, so no barrier is needed for p;
+//   * reductions are per-warp partials stored into every CTA's shared memory and summed in one fixed order
+//     (every thread of the cluster gets bit-identical scalars); the only synchronisation is the hardware
+//     cluster barrier, TWO per iteration (the two dependent reductions of PCG).
 // If the problem does not fit (shared-memory capacity, 16-bit offsets) the kernel leaves *cluster_done == 0
 // and the persistent grid kernel of k_pcg.cu, launched right after it, does the solve; when it fits, that
 // kernel sees *cluster_done == 1 and returns at once. No host round trip decides anything.
@@ -29,16 +31,18 @@ constexpr int CL_WARPS   = CL_THREADS / 32;
 constexpr int CL_MAX     = 16; // largest cluster tried
 
 struct ClusterLayout { // byte offsets into the dynamic shared memory of one CTA
-    int pfull, val, col, diag, invd, x, r, ap, slice_pap, off, total;
+    int pwin, zwin, val, col, diag, invd, x, r, ap, slice_pap, off, total;
 };
 
 __device__ __forceinline__ int align16(int b) { return (b + 15) & ~15; }
 
-// rows_pad: rows of the whole system padded to slices; own_slices: slices of this CTA; entries: its stored slots * 32
-__device__ __forceinline__ ClusterLayout make_layout(int rows_pad, int own_slices, int entries) {
+// window: rows of p this CTA reads (its own rows and the columns of its block); own_slices: its slices;
+// entries: its stored slots * 32
+__device__ __forceinline__ ClusterLayout make_layout(int window, int own_slices, int entries) {
     ClusterLayout L;
     int b = 0;
-    L.pfull = b; b = align16(b + rows_pad * 8);
+    L.pwin = b; b = align16(b + window * 8);
+    L.zwin = b; b = align16(b + window * 8);
     L.val = b; b = align16(b + entries * 8);
     L.col = b; b = align16(b + entries * 2);
     const int own_rows = own_slices * 32;
@@ -53,76 +57,92 @@ __device__ __forceinline__ ClusterLayout make_layout(int rows_pad, int own_slice
     return L;
 }
 
-// Deterministic CTA-wide sum of two values, result in every thread (fixed shuffle tree, fixed warp order).
-__device__ __forceinline__ void cta_sum2(double& a, double& b, double* sh /* 2 * CL_WARPS + 2 */) {
+// CTA-wide (sum, min, max) of three ints, result in every thread.
+__device__ __forceinline__ void cta_sum_min_max(int& sum, int& mn, int& mx, int* shi /* 3 * CL_WARPS */) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
-        a += __shfl_xor_sync(0xffffffffu, a, o);
-        b += __shfl_xor_sync(0xffffffffu, b, o);
+        sum += __shfl_xor_sync(0xffffffffu, sum, o);
+        mn = min(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+        mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
     }
     __syncthreads();
     if (lane == 0) {
-        sh[warp]            = a;
-        sh[CL_WARPS + warp] = b;
+        shi[warp]                = sum;
+        shi[CL_WARPS + warp]     = mn;
+        shi[2 * CL_WARPS + warp] = mx;
     }
     __syncthreads();
-    if (threadIdx.x == 0) {
-        double sa = 0.0, sb = 0.0;
-        for (int w = 0; w < CL_WARPS; w++) {
-            sa += sh[w];
-            sb += sh[CL_WARPS + w];
-        }
-        sh[2 * CL_WARPS]     = sa;
-        sh[2 * CL_WARPS + 1] = sb;
+    sum = 0;
+    for (int w = 0; w < CL_WARPS; w++) {
+        sum += shi[w];
+        mn = min(mn, shi[CL_WARPS + w]);
+        mx = max(mx, shi[2 * CL_WARPS + w]);
     }
-    __syncthreads();
-    a = sh[2 * CL_WARPS];
-    b = sh[2 * CL_WARPS + 1];
 }
 
 __global__ void __launch_bounds__(CL_THREADS, 1) pcg_cluster_kernel(Params P, int smem_bytes, int iteration_cap) {
     cg::cluster_group cluster = cg::this_cluster();
     extern __shared__ __align__(16) unsigned char dyn[];
-    __shared__ double sh[2 * CL_WARPS + 2];
-    __shared__ double red[2][CL_MAX][2]; // [exchange parity][rank][value]; written by every CTA through DSMEM
-    __shared__ int nofit[CL_MAX];        // written by every CTA through DSMEM
+    __shared__ int shi[3 * CL_WARPS];
+    // [exchange parity][source rank][source warp][value]: every warp of every CTA stores its partial here, in
+    // every CTA, through DSMEM; summed by every warp in the same fixed order after the cluster barrier
+    __shared__ double red[2][CL_MAX][CL_WARPS][2];
+    __shared__ int meta[CL_MAX][3]; // per rank: does-not-fit flag, window [lo, hi); written through DSMEM
 
     const int C = (int) cluster.num_blocks(), rank = (int) cluster.block_rank();
     unsigned long long t_begin;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_begin));
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int n = *P.n_active;
-    const int slices = (n + 31) >> 5, rows_pad = slices * 32;
+    const int slices = (n + 31) >> 5;
     const int per = (slices + C - 1) / C;
     const int s0 = min(rank * per, slices), s1 = min(s0 + per, slices), own = s1 - s0;
     const int row0 = s0 * 32, own_rows = own * 32;
 
-    // ---- does it fit? every CTA measures its block; all agree through DSMEM before anything is written
-    double ent = 0.0, dummy = 0.0;
-    for (int s = s0 + (int) threadIdx.x; s < s1; s += CL_THREADS) ent += (double) P.ell_width[s];
-    cta_sum2(ent, dummy, sh);
-    const int entries = (int) ent * 32;
-    const ClusterLayout L = make_layout(rows_pad, own, entries);
+    // ---- size of the block and the window of p it reads; does it fit? all CTAs agree through DSMEM
+    int ent = 0, wlo = row0, whi = row0 + own_rows - 1;
+    for (int s = s0 + (int) threadIdx.x; s < s1; s += CL_THREADS) {
+        ent += P.ell_width[s];
+        wlo = min(wlo, P.ell_cmin[s]);
+        whi = max(whi, P.ell_cmax[s]);
+    }
+    cta_sum_min_max(ent, wlo, whi, shi);
+    wlo &= ~31;                             // whole slices: rows of a slice beyond n are padding with p = 0
+    whi = own > 0 ? ((whi + 32) & ~31) : wlo; // exclusive
+    const int window = whi - wlo, entries = ent * 32;
+    const ClusterLayout L = make_layout(window, own, entries);
     const int bad = (L.total > smem_bytes || *P.ell_wide != 0 || n > 32767) ? 1 : 0;
-    if (threadIdx.x < (unsigned) C) *cluster.map_shared_rank(&nofit[rank], threadIdx.x) = bad;
+    if (threadIdx.x < (unsigned) C) {
+        int* m = cluster.map_shared_rank(&meta[rank][0], threadIdx.x);
+        m[0] = bad;
+        m[1] = wlo;
+        m[2] = whi;
+    }
     cluster.sync();
     int any_bad = 0;
-    for (int q = 0; q < C; q++) any_bad |= nofit[q];
+    for (int q = 0; q < C; q++) any_bad |= meta[q][0];
     if (any_bad) return; // uniform over the cluster; *cluster_done stays 0 -> the grid kernel solves
 
-    double* pfull  = reinterpret_cast<double*>(dyn + L.pfull);
-    double* val    = reinterpret_cast<double*>(dyn + L.val);
-    short* col     = reinterpret_cast<short*>(dyn + L.col);
-    double* diag   = reinterpret_cast<double*>(dyn + L.diag);
-    double* invd   = reinterpret_cast<double*>(dyn + L.invd);
-    double* x      = reinterpret_cast<double*>(dyn + L.x);
-    double* r      = reinterpret_cast<double*>(dyn + L.r);
-    double* ap     = reinterpret_cast<double*>(dyn + L.ap);
-    double* spap   = reinterpret_cast<double*>(dyn + L.slice_pap);
-    int* off       = reinterpret_cast<int*>(dyn + L.off);
+    double* pwin = reinterpret_cast<double*>(dyn + L.pwin) - wlo; // indexed by global row
+    double* zwin = reinterpret_cast<double*>(dyn + L.zwin) - wlo;
+    double* val  = reinterpret_cast<double*>(dyn + L.val);
+    short* col   = reinterpret_cast<short*>(dyn + L.col);
+    double* diag = reinterpret_cast<double*>(dyn + L.diag);
+    double* invd = reinterpret_cast<double*>(dyn + L.invd);
+    double* x    = reinterpret_cast<double*>(dyn + L.x);
+    double* r    = reinterpret_cast<double*>(dyn + L.r);
+    double* ap   = reinterpret_cast<double*>(dyn + L.ap);
+    double* spap = reinterpret_cast<double*>(dyn + L.slice_pap);
+    int* off     = reinterpret_cast<int*>(dyn + L.off);
+    // the p / z windows of CTA q, indexed by global row (valid inside q's window [meta[q][1], meta[q][2]) only);
+    // every CTA's layout starts with pwin at offset 0 and zwin right after a window of ITS OWN size
+    auto peer_p = [&](int q) -> double* { return reinterpret_cast<double*>(cluster.map_shared_rank(dyn, q)) - meta[q][1]; };
+    auto peer_z = [&](int q) -> double* {
+        return reinterpret_cast<double*>(cluster.map_shared_rank(dyn, q) + align16((meta[q][2] - meta[q][1]) * 8)) - meta[q][1];
+    };
 
-    // ---- load the block: slot offsets (serial prefix over <= a few hundred slices), then the matrix
+    // ---- load the block: slot offsets (serial prefix over a few slices), then the matrix
     if (threadIdx.x == 0) {
         int acc = 0;
         for (int s = 0; s < own; s++) {
@@ -131,7 +151,11 @@ __global__ void __launch_bounds__(CL_THREADS, 1) pcg_cluster_kernel(Params P, in
         }
         off[own] = acc;
     }
-    __syncthreads();
+    for (int j = wlo + (int) threadIdx.x; j < whi; j += CL_THREADS) { // rows nobody owns (beyond n) stay 0
+        pwin[j] = 0.0;
+        zwin[j] = 0.0;
+    }
+    cluster.sync(); // windows are cleared everywhere before any CTA stores into them
     for (int sl = warp; sl < own; sl += CL_WARPS) {
         const int s = s0 + sl, w = (off[sl + 1] - off[sl]) >> 5;
         const size_t g = (size_t) s * (size_t) P.K * 32u;
@@ -140,45 +164,79 @@ __global__ void __launch_bounds__(CL_THREADS, 1) pcg_cluster_kernel(Params P, in
             col[off[sl] + k * 32 + lane] = P.ell_col16[g + (size_t) k * 32 + lane];
         }
     }
+    // store v as row `row` of p (which = 0) or z (which = 1) in every CTA whose window holds that row
+    // (windows grow with the rank, so the destinations of a row are a contiguous range of ranks; the range of
+    // the thread's first row is kept in registers, further rows of large blocks recompute it)
+    auto dest_range = [&](int row, int& qa, int& qb) {
+        qa = C;
+        qb = -1;
+        for (int q = 0; q < C; q++)
+            if (row >= meta[q][1] && row < meta[q][2]) {
+                qa = min(qa, q);
+                qb = max(qb, q);
+            }
+    };
+    int my_qa, my_qb;
+    dest_range(row0 + (int) threadIdx.x, my_qa, my_qb);
+    auto broadcast = [&](int row, double v, int which) {
+        int qa = my_qa, qb = my_qb;
+        if (row != row0 + (int) threadIdx.x) dest_range(row, qa, qb);
+        for (int q = qa; q <= qb; q++)
+            if (row >= meta[q][1] && row < meta[q][2]) (which ? peer_z(q) : peer_p(q))[row] = v;
+    };
     // setup: x = 0, r = b, invdiag, p = invdiag r (0 beyond n); |b|^2 and r.p
     double l0 = 0.0, l1 = 0.0;
     for (int i = threadIdx.x; i < own_rows; i += CL_THREADS) {
         const int row = row0 + i;
-        double d = 0.0, id = 1.0, bi = 0.0, pi = 0.0;
+        double d = 0.0, id = 1.0, bi = 0.0;
         if (row < n) {
             bi = P.rhs[row];
             d  = P.diag[row];
             id = d != 0.0 ? 1.0 / d : 1.0;
-            pi = id * bi;
+            const double pi = id * bi;
             l0 += bi * bi;
             l1 += bi * pi;
+            broadcast(row, pi, 0);
         }
         diag[i] = d; invd[i] = id; x[i] = 0.0; r[i] = bi; ap[i] = 0.0;
-        for (int q = 0; q < C; q++) cluster.map_shared_rank(pfull, q)[row] = pi;
     }
     // particle slots that are not rows of the system keep pressure 0 (as the grid kernel's setup does)
     for (int i = n + rank * CL_THREADS + (int) threadIdx.x; i < P.N; i += C * CL_THREADS) P.S.p[i] = 0.0;
 
     int parity = 0;
-    // all-CTA sum of (a, b): partial -> every CTA's red[parity][rank] -> cluster barrier -> rank-order sum
+    // All-CTA sum of (a, b): every warp reduces its lanes and stores the pair into red[parity][rank][warp] of
+    // EVERY CTA (lane q stores to rank q); after the cluster barrier every warp adds the C x 16 pairs in the
+    // same fixed order (lane-strided, then the shuffle tree) -> bit-identical scalars in every thread of the
+    // cluster, and a single barrier per reduction. The barrier also publishes the window stores made before it.
+    // (Measured alternative: per-warp remote mbarrier arrivals instead of barrier.cluster — 25 % slower.)
     auto exchange = [&](double& a, double& b) {
-        cta_sum2(a, b, sh);
-        if (threadIdx.x < (unsigned) C) {
-            double* dst = cluster.map_shared_rank(&red[parity][rank][0], threadIdx.x);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            a += __shfl_xor_sync(0xffffffffu, a, o);
+            b += __shfl_xor_sync(0xffffffffu, b, o);
+        }
+        if (lane < C) {
+            double* dst = cluster.map_shared_rank(&red[parity][rank][warp][0], lane);
             dst[0] = a;
             dst[1] = b;
         }
         cluster.sync();
         double sa = 0.0, sb = 0.0;
-        for (int q = 0; q < C; q++) {
-            sa += red[parity][q][0];
-            sb += red[parity][q][1];
+        const double* src = &red[parity][0][0][0];
+        for (int e = lane; e < C * CL_WARPS; e += 32) {
+            sa += src[2 * e];
+            sb += src[2 * e + 1];
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            sa += __shfl_xor_sync(0xffffffffu, sa, o);
+            sb += __shfl_xor_sync(0xffffffffu, sb, o);
         }
         a = sa;
         b = sb;
         parity ^= 1;
     };
-    exchange(l0, l1); // also publishes the p replicas and orders the matrix load before the first sweep
+    exchange(l0, l1); // also publishes the p windows and orders the matrix load before the first sweep
     const double rhsNorm2 = l0;
     double absNew = l1, residualNorm2 = rhsNorm2;
     bool done = false;
@@ -190,16 +248,19 @@ __global__ void __launch_bounds__(CL_THREADS, 1) pcg_cluster_kernel(Params P, in
     if (!done && residualNorm2 < threshold) done = true;
     const int maxIters = iteration_cap > 0 ? iteration_cap : 2 * P.N;
     int it = 0;
+    long long cyc[4] = {0, 0, 0, 0}, c0 = clock64(), c1;
+#define CL_TICK(slot) do { c1 = clock64(); cyc[slot] += c1 - c0; c0 = c1; } while (0)
     while (!done && it < maxIters) {
-        // ---- sweep A: ap = A p; p.ap per slice, then per CTA in slice order
+        // ---- sweep A: ap = A p; p.ap per slice
         for (int sl = warp; sl < own; sl += CL_WARPS) {
             const int base = (s0 + sl) * 32, w = (off[sl + 1] - off[sl]) >> 5, o = off[sl];
-            const double pr = pfull[base + lane];
+            const double* pb = pwin + base;
+            const double pr  = pb[lane];
             double sum = diag[sl * 32 + lane] * pr;
             for (int k = 0; k < w; k += 4) { // widths are multiples of 4: four gathers in flight, adds in slot order
-                const int c0 = col[o + (k + 0) * 32 + lane], c1 = col[o + (k + 1) * 32 + lane];
-                const int c2 = col[o + (k + 2) * 32 + lane], c3 = col[o + (k + 3) * 32 + lane];
-                const double p0 = pfull[base + c0], p1 = pfull[base + c1], p2 = pfull[base + c2], p3 = pfull[base + c3];
+                const int k0 = col[o + (k + 0) * 32 + lane], k1 = col[o + (k + 1) * 32 + lane];
+                const int k2 = col[o + (k + 2) * 32 + lane], k3 = col[o + (k + 3) * 32 + lane];
+                const double p0 = pb[k0], p1 = pb[k1], p2 = pb[k2], p3 = pb[k3];
                 const double v0 = val[o + (k + 0) * 32 + lane], v1 = val[o + (k + 1) * 32 + lane];
                 const double v2 = val[o + (k + 2) * 32 + lane], v3 = val[o + (k + 3) * 32 + lane];
                 sum += v0 * p0; sum += v1 * p1; sum += v2 * p2; sum += v3 * p3;
@@ -211,40 +272,43 @@ __global__ void __launch_bounds__(CL_THREADS, 1) pcg_cluster_kernel(Params P, in
             if (lane == 0) spap[sl] = v;
         }
         __syncthreads();
+        CL_TICK(0);
         double lpap = 0.0, unused = 0.0;
         for (int sl = threadIdx.x; sl < own; sl += CL_THREADS) lpap += spap[sl];
         exchange(lpap, unused);
         const double alpha = absNew / lpap;
-        // ---- sweep B: x += alpha p; r -= alpha ap; |r|^2; r.z
+        CL_TICK(3);
+        // ---- sweep B: x += alpha p; r -= alpha ap; |r|^2; r.z; z = invdiag r goes to every window holding the row
         double lrr = 0.0, lrz = 0.0;
         for (int i = threadIdx.x; i < own_rows; i += CL_THREADS) {
-            if (row0 + i < n) {
+            const int row = row0 + i;
+            if (row < n) {
                 const double ri = r[i] - alpha * ap[i];
-                x[i] += alpha * pfull[row0 + i];
+                x[i] += alpha * pwin[row];
                 r[i] = ri;
+                const double zi = invd[i] * ri;
                 lrr += ri * ri;
-                lrz += ri * (invd[i] * ri);
+                lrz += ri * zi;
+                broadcast(row, zi, 1);
             }
         }
-        exchange(lrr, lrz);
+        CL_TICK(1);
+        exchange(lrr, lrz); // its barrier publishes the z windows
         residualNorm2 = lrr;
         if (residualNorm2 < threshold) break;
         const double beta = lrz / absNew;
         absNew = lrz;
-        // ---- sweep C: p = z + beta p, written into every CTA's replica
-        for (int i = threadIdx.x; i < own_rows; i += CL_THREADS) {
-            if (row0 + i < n) {
-                const double v = invd[i] * r[i] + beta * pfull[row0 + i];
-                for (int q = 0; q < C; q++) cluster.map_shared_rank(pfull, q)[row0 + i] = v;
-            }
-        }
+        CL_TICK(3);
+        // ---- sweep C: p = z + beta p on the whole window, locally (no third barrier)
+        for (int j = wlo + (int) threadIdx.x; j < whi; j += CL_THREADS) pwin[j] = zwin[j] + beta * pwin[j];
         it++;
-        cluster.sync();
+        __syncthreads();
+        CL_TICK(2);
     }
     for (int i = threadIdx.x; i < own_rows; i += CL_THREADS)
         if (row0 + i < n) P.S.p[row0 + i] = x[i];
     if (rank == 0 && threadIdx.x == 0) {
-        for (int k = 0; k < 4; k++) P.stats->cg_cycles[k] = 0;
+        for (int k = 0; k < 4; k++) P.stats->cg_cycles[k] = cyc[k];
         P.stats->cg_iterations   = it;
         P.stats->pad[0]          = 1;
         P.stats->pad[1]          = 1;
@@ -267,7 +331,7 @@ int mpsb_pcg_cluster_configure(mpsb_handle* h) {
     h->cl_smem = 0;
     int max_optin = 0;
     if (cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device) != cudaSuccess) return 0;
-    const int smem = max_optin - 8 * 1024; // static shared memory of the kernel + a margin
+    const int smem = max_optin - 12 * 1024; // the kernel's static shared memory (8.4 KB) + a margin
     if (cudaFuncSetAttribute(pcg_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return 0;
     cudaFuncSetAttribute(pcg_cluster_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
     for (int c : {16, 8, 4, 2}) {
@@ -304,7 +368,8 @@ int mpsb_launch_pcg_cluster(mpsb_handle* h) {
     int csize = 1;
     while (csize < h->cl_size) {
         const int per = (slices + csize - 1) / csize;
-        const long bytes = (long) slices * 32 * 8 + (long) per * 32 * ((long) width * 10 + 48) + 1024;
+        const int win    = per + 64 < slices ? per + 64 : slices; // own slices + the cell rows either side
+        const long bytes = (long) win * 32 * 16 + (long) per * 32 * ((long) width * 10 + 48) + 1024;
         if (bytes <= h->cl_smem) break;
         csize *= 2;
     }
