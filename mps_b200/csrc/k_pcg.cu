@@ -35,9 +35,6 @@
 
 namespace cg = cooperative_groups;
 
-#ifndef PCG_PIPE
-#define PCG_PIPE 0   // 1: software-pipelined sweep-A consumer (gathers of the next stage ahead of the FMAs); measured slower
-#endif
 #ifndef PCG_NSTAGES
 #define PCG_NSTAGES 2
 #endif
@@ -69,7 +66,7 @@ struct __align__(128) Stage {
 struct __align__(16) StageMeta {
     int slice;
     int nslots;
-    int first; // first chunk of the slice (start the row sum from diag * p)
+    int first; // bit 0: first chunk of the slice (start the row sum from diag * p); bit 1: the slice may read a peer's rows
     int last;  // last chunk of the slice (store ap, accumulate p.ap)
 };
 struct Smem {
@@ -286,6 +283,42 @@ __device__ __forceinline__ void xchg_sum2(const Params& P, double (*xr)[2], doub
     }
 }
 
+// The exchange that ends sweep C, split in two so that nothing on this rank waits for NVLink (see HaloWait):
+//   local barrier   every CTA fences at GPU scope and arrives; the last one releases this rank's own flag;
+//                   every CTA waits for that flag only and goes on to sweep A.
+//   publication     off the critical path: a CTA that stored halo rows into a peer's p vector fences at system
+//                   scope, then every CTA arrives on a second counter; the last one fences and stores the epoch
+//                   into the peers' inboxes. Peers look at it only when a warp reaches a boundary slice.
+__device__ __forceinline__ void publish_split(const Params& P, Xchg& xs, unsigned long long& publishes, bool pushed) {
+    const PeerLinks& L = P.L;
+    const unsigned long long nblocks = gridDim.x;
+    xs.epoch++;
+    xs.count++;
+    publishes++;
+    const int any_pushed = __syncthreads_or(pushed ? 1 : 0); // also: the CTA's stores precede thread 0's fences
+    if (threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(L.arrive, 1ull) + 1ull == xs.count * nblocks) {
+            __threadfence();
+            asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(L.flag + L.rank), "l"(xs.epoch) : "memory");
+        }
+        if (any_pushed) __threadfence_system();
+        if (atomicAdd(L.arrive + 1, 1ull) + 1ull == publishes * nblocks) {
+            __threadfence_system();
+            for (int q = 0; q < L.world; q++)
+                if (q != L.rank) asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(L.peer_flag[q] + L.rank), "l"(xs.epoch) : "memory");
+        }
+        const unsigned long long t0 = global_timer_ns();
+        unsigned spins = 0;
+        unsigned long long seen;
+        do {
+            asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(seen) : "l"(L.flag + L.rank) : "memory");
+            if ((++spins & 1023u) == 0) xchg_timeout(P, t0);
+        } while (seen < xs.epoch);
+    }
+    __syncthreads();
+}
+
 // Ring bookkeeping of one warp; serial numbers keep running across sweeps so the mbarrier phase
 // parity of stage (serial % STAGES) is (serial / STAGES) & 1.
 struct Pipe {
@@ -302,17 +335,38 @@ constexpr int PCG_BATCH = PCG_NBATCH; // slices taken from the global queue per 
 // into slice_pap[]; the caller sums that array in a fixed order. Rows of a slice beyond n carry diag 0 /
 // padding only and p = 0 there.
 // The sweep covers slices [sbeg, nslices) (a rank's row block; sbeg = 0 on one GPU).
+// MULTI only: the order in which a rank walks its slices and what the slices at the ends of its block wait for.
+// The exchange that ends sweep C is split: every CTA waits only for its OWN rank's flag (the local barrier),
+// sweep A starts at once in the MIDDLE of the block (tickets are rotated by `shift`), and a warp waits for the
+// peers' flags — the halo rows of p they stored into this rank's vector — only when it reaches a slice outside
+// [gap_lo, gap_hi), i.e. one whose columns can leave the block. By then the flags have long arrived, so the
+// NVLink latency of the halo publication is hidden behind the interior of the sweep.
+struct HaloWait {
+    int shift;                       // ticket v walks slice sbeg + (v - sbeg + shift) mod (nslices - sbeg)
+    int gap_lo, gap_hi;              // slices [gap_lo, gap_hi) read no row of another rank
+    const unsigned long long* flags; // this rank's inbox flags
+    unsigned long long epoch;        // the publishing exchange the halo rows belong to
+    int world;
+};
+
 template <bool C16>
 __device__ __forceinline__ void spmv_sweep(const Params& P, Smem& sm, Pipe& pipe, int sbeg, int nslices, const double* p,
-                                           double* ap, unsigned* ticket, double* slice_pap) {
+                                           double* ap, unsigned* ticket, double* slice_pap, const HaloWait& hw) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const size_t K = (size_t) P.K;
+    const int nsl_total = nslices - sbeg;
+    auto rot = [&](int v) -> int { // ticket -> slice
+        int x = v - sbeg + hw.shift;
+        if (x >= nsl_total) x -= nsl_total;
+        return sbeg + x;
+    };
+    bool halo_ready = false;
     auto take = [&]() -> int { // lane 0 holds the result; shuffled when needed
         int v = 0;
         if (lane == 0) v = sbeg + (int) atomicAdd(ticket, (unsigned) PCG_BATCH);
         return v;
     };
-    auto widths = [&](int s0) -> int { return (lane < PCG_BATCH && s0 + lane < nslices) ? P.ell_width[s0 + lane] : 0; };
+    auto widths = [&](int s0) -> int { return (lane < PCG_BATCH && s0 + lane < nslices) ? P.ell_width[rot(s0 + lane)] : 0; };
     // batch pipeline: cur (being issued), nxt (id known, widths loading), t2 (ticket in flight)
     int cur = __shfl_sync(0xffffffffu, take(), 0);
     int cur_w = widths(cur);
@@ -323,13 +377,14 @@ __device__ __forceinline__ void spmv_sweep(const Params& P, Smem& sm, Pipe& pipe
     int pw = __shfl_sync(0xffffffffu, cur_w, 0);
     auto produce = [&]() -> bool {
         if (cur + pi >= nslices || pipe.issued - pipe.consumed >= (unsigned) PCG_STAGES) return false;
-        const int slice = cur + pi;
+        const int slice = rot(cur + pi);
         const int nsl   = min(PCG_CH, pw - pk);
+        const int halo  = (slice < hw.gap_lo || slice >= hw.gap_hi) ? 2 : 0;
         const bool first = pk == 0, last = pk + nsl >= pw;
         const unsigned st = pipe.issued % PCG_STAGES;
         if (lane == 0) {
             Stage& S = sm.stage[warp][st];
-            sm.meta[warp][st] = StageMeta{slice, nsl, first ? 1 : 0, last ? 1 : 0};
+            sm.meta[warp][st] = StageMeta{slice, nsl, (first ? 1 : 0) | halo, last ? 1 : 0};
             unsigned long long* bar = &sm.full[warp][st];
             mbar_arrive_expect_tx(bar, (first ? 256u : 0u) + (unsigned) nsl * (C16 ? 320u : 384u));
             if (first) bulk_g2s(S.diag, P.diag + (size_t) slice * 32, 256u, bar);
@@ -357,80 +412,6 @@ bulk_g2s(S.val, P.ell_val + off, (unsigned) nsl * 256u, bar);
     };
     double sum = 0.0, pr = 0.0;
     int row = 0;
-#if PCG_PIPE
-    // Software-pipelined consumer: the column loads and p[col] gathers of stage j+1 are issued BEFORE the
-    // multiply-adds of stage j, so the gather latency (L1 miss -> L2 under a saturated HBM stream) overlaps
-    // the arithmetic, the ring bookkeeping and the TMA issue instead of heading every stage's dependent
-    // chain. Two register sets (ga/gb) alternate; the summation order per row is unchanged (slot order).
-    auto fetch = [&](unsigned serial, double (&g)[PCG_CH], double& gpr) {
-        const unsigned st = serial % PCG_STAGES, parity = (serial / PCG_STAGES) & 1u;
-        const StageMeta m = sm.meta[warp][st];
-        const Stage& S    = sm.stage[warp][st];
-        if (m.first) gpr = p[m.slice * 32 + lane];
-        mbar_wait(&sm.full[warp][st], parity);
-#pragma unroll
-        for (int k = 0; k < PCG_CH; k++) {
-            int c = 0;
-            if (k < m.nslots) {
-                if (C16) c = m.slice * 32 + (int) reinterpret_cast<const short*>(S.col)[k * 32 + lane];
-                else c = S.col[k * 32 + lane];
-            }
-            g[k] = p[c];
-        }
-    };
-    auto compute = [&](double (&g)[PCG_CH], double gpr) {
-        const unsigned st = pipe.consumed % PCG_STAGES;
-        const StageMeta m = sm.meta[warp][st];
-        const Stage& S    = sm.stage[warp][st];
-        if (m.first) {
-            row = m.slice * 32 + lane;
-            pr  = gpr;
-            sum = S.diag[lane] * pr;
-        }
-#pragma unroll
-        for (int k = 0; k < PCG_CH; k += 4) {
-            if (k < m.nslots) {
-                double v0 = S.val[(k + 0) * 32 + lane], v1 = S.val[(k + 1) * 32 + lane];
-                double v2 = S.val[(k + 2) * 32 + lane], v3 = S.val[(k + 3) * 32 + lane];
-                sum += v0 * g[k + 0]; sum += v1 * g[k + 1]; sum += v2 * g[k + 2]; sum += v3 * g[k + 3];
-            }
-        }
-        if (m.last) {
-            ap[row] = sum;
-            double v = pr * sum;
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-            if (lane == 0) slice_pap[m.slice] = v;
-        }
-        __syncwarp(); // every lane is done with the stage before lane 0 refills it
-        pipe.consumed++;
-    };
-    double ga[PCG_CH], gb[PCG_CH], gpa = 0.0, gpb = 0.0;
-    while (produce()) {}
-    if (pipe.consumed == pipe.issued) return;
-    __syncwarp(); // lane 0's meta of freshly issued stages is visible to the warp
-    fetch(pipe.consumed, ga, gpa);
-    for (;;) {
-        bool ahead = pipe.consumed + 1u < pipe.issued;
-        if (ahead) fetch(pipe.consumed + 1u, gb, gpb);
-        compute(ga, gpa);
-        while (produce()) {}
-        __syncwarp();
-        if (!ahead) {
-            if (pipe.consumed == pipe.issued) break;
-            fetch(pipe.consumed, gb, gpb);
-        }
-        ahead = pipe.consumed + 1u < pipe.issued;
-        if (ahead) fetch(pipe.consumed + 1u, ga, gpa);
-        compute(gb, gpb);
-        while (produce()) {}
-        __syncwarp();
-        if (!ahead) {
-            if (pipe.consumed == pipe.issued) break;
-            fetch(pipe.consumed, ga, gpa);
-        }
-    }
-#else
     for (;;) {
         while (produce()) {}
         if (pipe.consumed == pipe.issued) break;
@@ -438,12 +419,23 @@ bulk_g2s(S.val, P.ell_val + off, (unsigned) nsl * 256u, bar);
         const unsigned st = pipe.consumed % PCG_STAGES, parity = (pipe.consumed / PCG_STAGES) & 1u;
         const StageMeta m = sm.meta[warp][st];
         const Stage& S    = sm.stage[warp][st];
-        if (m.first) { // own-row p: issued before the wait so its latency hides behind the TMA
+        if (m.first & 1) { // own-row p: issued before the wait so its latency hides behind the TMA
             row = m.slice * 32 + lane;
             pr  = p[row];
         }
         mbar_wait(&sm.full[warp][st], parity);
-        if (m.first) sum = S.diag[lane] * pr;
+        if ((m.first & 2) && !halo_ready) { // first slice of this warp that may read a peer's rows
+            if (lane == 0) {
+                const unsigned long long t0 = global_timer_ns();
+                unsigned spins = 0;
+                for (int q = 0; q < hw.world; q++)
+                    while (ld_acquire_sys(hw.flags + q) < hw.epoch)
+                        if ((++spins & 1023u) == 0) xchg_timeout(P, t0);
+            }
+            __syncwarp();
+            halo_ready = true;
+        }
+        if (m.first & 1) sum = S.diag[lane] * pr;
         double g[PCG_CH]; // all gathers of the stage in flight together
 #pragma unroll
         for (int k = 0; k < PCG_CH; k++) {
@@ -472,7 +464,6 @@ bulk_g2s(S.val, P.ell_val + off, (unsigned) nsl * 256u, bar);
         __syncwarp(); // every lane is done with the stage before lane 0 refills it
         pipe.consumed++;
     }
-#endif
 }
 
 // MULTI = false: one GPU, rows [0, n). MULTI = true: this rank's row block; see the file header.
@@ -534,6 +525,7 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
     // its row block [need_lo, need_hi]; the rows of mine inside a peer's extent are pushed to that peer
     // whenever p changes (here and in sweep C). push_gap_* bracket the rows nobody else needs.
     int push_gap_lo = row_lo, push_gap_hi = row_hi;
+    unsigned long long halo_epoch = 0ull; // epoch of the last exchange that published halo rows
     if (MULTI) {
         double cmn = DBL_MAX, cmx = -DBL_MAX;
         for (int sl = sl_lo + tid; sl < sl_hi; sl += stride) {
@@ -566,6 +558,7 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
             for (int i = sm.need[q][0] + tid; i < sm.need[q][1]; i += stride) dst[i] = p[i];
         }
         xchg_all<XCHG_PUBLISH>(P, xs, 0.0, 0.0, part0, part1, sh, &sm.flag, sm.xr); // the halo rows are visible before any sweep A
+        halo_epoch = xs.epoch; // flags carry the epochs of PUBLISHING exchanges only
     }
     double rhsNorm2, absNew;
     if (MULTI) {
@@ -596,12 +589,26 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
     const bool odd_tail = ((act_hi - row_lo) & 1) != 0; // row act_hi - 1 is left over
 
     // MULTI: store row i of the new p into the p vector of every peer that reads it
+    bool did_push = false;              // this thread stored into a peer's p vector in the running sweep C
+    unsigned long long publishes = 0ull; // split publications so far in this launch (second arrival counter)
     auto push_row = [&](int i, double v) {
         if (i >= push_gap_lo && i < push_gap_hi) return;
         for (int q = 0; q < W; q++)
-            if (i >= sm.need[q][0] && i < sm.need[q][1]) P.L.peer_p[q][i] = v;
+            if (i >= sm.need[q][0] && i < sm.need[q][1]) {
+                P.L.peer_p[q][i] = v;
+                did_push = true;
+            }
     };
 
+    // sweep A's walk (see HaloWait): single GPU = natural order, nothing to wait for
+    HaloWait hw{0, sl_lo, sl_hi, nullptr, 0ull, 1};
+    if (MULTI) {
+        hw.shift  = (sl_hi - sl_lo) / 2;
+        hw.gap_lo = (max(push_gap_lo, row_lo) + 31) >> 5;
+        hw.gap_hi = min(push_gap_hi, row_hi) >> 5;
+        hw.flags  = P.L.flag;
+        hw.world  = W;
+    }
     // pairs of active rows at the high end of the block that some peer reads (sweep C handles them first)
     const int high_pairs = MULTI ? max(0, min(pair_hi - pair_lo, pair_hi - (max(push_gap_hi, row_lo) >> 1))) : 0;
     long long cyc[4] = {0, 0, 0, 0}, t0 = clock64(), t1;
@@ -609,28 +616,31 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
     while (!done && it < maxIters) {
         // ---- sweep A: ap = A p, p.ap ----
         unsigned* ticket = tickets + (it & 1);
-        if (col16) spmv_sweep<true>(P, sm, pipe, sl_lo, sl_hi, p, ap, ticket, P.cg_slice_pap);
-        else spmv_sweep<false>(P, sm, pipe, sl_lo, sl_hi, p, ap, ticket, P.cg_slice_pap);
+        if (MULTI) hw.epoch = halo_epoch;
+        if (col16) spmv_sweep<true>(P, sm, pipe, sl_lo, sl_hi, p, ap, ticket, P.cg_slice_pap, hw);
+        else spmv_sweep<false>(P, sm, pipe, sl_lo, sl_hi, p, ap, ticket, P.cg_slice_pap, hw);
         __syncthreads();
         PCG_TICK(0);
-        grid.sync();
-        // p.ap = sum of the per-slice partials in a fixed order: this CTA's fixed range, then all CTAs
-        if (tid == 0) tickets[(it + 1) & 1] = 0u; // the other counter is idle until the next sweep A
-        double lpap = 0.0, dummy = 0.0;
-        {
-            const int nsl = sl_hi - sl_lo, per = (nsl + nblocks - 1) / nblocks;
-            const int lo = sl_lo + blockIdx.x * per, hi = min(lo + per, sl_hi);
-            for (int i = lo + (int) threadIdx.x; i < hi; i += PCG_THREADS) lpap += __ldcg(P.cg_slice_pap + i);
-        }
         double pap, unused;
-        if (MULTI) {
-            xchg_all<XCHG_SUM>(P, xs, lpap, dummy, part0, part1, sh, &sm.flag, sm.xr);
-            xchg_sum2(P, sm.xr, pap, unused);
-        } else {
-            block_sum2(lpap, dummy, sh);
-            if (threadIdx.x == 0) part0[blockIdx.x] = lpap;
+        {
             grid.sync();
-            grid_sum2(part0, part0, nblocks, pap, unused, sh);
+            // p.ap = sum of the per-slice partials in a fixed order: this CTA's fixed range, then all CTAs
+            if (tid == 0) tickets[(it + 1) & 1] = 0u; // the other counter is idle until the next sweep A
+            double lpap = 0.0, dummy = 0.0;
+            {
+                const int nsl = sl_hi - sl_lo, per = (nsl + nblocks - 1) / nblocks;
+                const int lo = sl_lo + blockIdx.x * per, hi = min(lo + per, sl_hi);
+                for (int i = lo + (int) threadIdx.x; i < hi; i += PCG_THREADS) lpap += __ldcg(P.cg_slice_pap + i);
+            }
+            if (MULTI) {
+                xchg_all<XCHG_SUM>(P, xs, lpap, dummy, part0, part1, sh, &sm.flag, sm.xr);
+                xchg_sum2(P, sm.xr, pap, unused);
+            } else {
+                block_sum2(lpap, dummy, sh);
+                if (threadIdx.x == 0) part0[blockIdx.x] = lpap;
+                grid.sync();
+                grid_sum2(part0, part0, nblocks, pap, unused, sh);
+            }
         }
         const double alpha = absNew / pap;
         PCG_TICK(3);
@@ -698,8 +708,11 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
         }
         it++;
         PCG_TICK(2);
-        if (MULTI) xchg_all<XCHG_PUBLISH>(P, xs, 0.0, 0.0, part0, part1, sh, &sm.flag, sm.xr); // barrier + publishes the halo rows
-        else grid.sync();
+        if (MULTI) { // local barrier + publication of the halo rows; the peers' flags are awaited inside sweep A
+            publish_split(P, xs, publishes, did_push);
+            did_push   = false;
+            halo_epoch = xs.epoch;
+        } else grid.sync();
         PCG_TICK(PCG_SPLIT_SYNC ? 2 : 3);
     }
     if (threadIdx.x == 0) { // per-CTA diagnostic rows behind the three reduction rows
@@ -748,7 +761,7 @@ void mpsb_launch_pcg(mpsb_handle* h) {
     if (grid < 1) grid = 1;
     int max_blocks = h->cg_max_blocks;
     cudaMemsetAsync(P.cg_partials + 8 * (size_t) max_blocks, 0, 8, h->stream); // the two slice-queue counters
-    if (multi) cudaMemsetAsync(P.L.arrive, 0, sizeof(unsigned long long), h->stream);
+    if (multi) cudaMemsetAsync(P.L.arrive, 0, 2 * sizeof(unsigned long long), h->stream); // both arrival counters
     int cap = h->cg_iteration_cap;
     void* args[] = {(void*) &P, (void*) &max_blocks, (void*) &cap};
     const void* fn = multi ? (const void*) pcg_kernel<true> : (const void*) pcg_kernel<false>;

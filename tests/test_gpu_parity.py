@@ -326,3 +326,22 @@ def test_cluster_solve_is_used_for_shipped_sizes_and_agrees_with_grid_solve(case
     assert U.rel_err(out[0][0], out[1][0]) <= TOL
     assert abs(out[0][1] - out[1][1]) <= max(2, 0.02 * out[1][1])
     assert out[0][3] <= 2.3e-16
+
+
+def test_graph_replayed_step_is_bitwise_the_directly_issued_step(monkeypatch):
+    """Small cases replay the step as one CUDA graph per pointer state (mpsb_api.cu); MPSB_NO_STEP_GRAPH=1 issues
+    the same launches directly. Same kernels, same order -> identical bits, incl. export steps (the second
+    graph variant) and the launch count."""
+    S, t, p, v = C.load_case("dambreak")
+    out = []
+    for no_graph in ("0", "1"):
+        monkeypatch.setenv("MPSB_NO_STEP_GRAPH", no_graph)
+        dev = capi.DeviceMPS(S, t, p, v)
+        dev.load_initial_state()
+        cour = [dev.step_forward(k % 7 == 0) for k in range(40)]
+        out.append((dev.download(), cour, dev.launch_count, dev.last_stats.cg_iterations, dev.last_stats.ms_solve))
+        dev.close()
+    for name in U.STATE_FIELDS:
+        assert np.array_equal(out[0][0][name], out[1][0][name]), name
+    assert out[0][1] == out[1][1] and out[0][2] == out[1][2] and out[0][3] == out[1][3]
+    assert out[0][4] > 0.0 and out[1][4] > 0.0  # the solve is timed on both paths
