@@ -7,6 +7,14 @@
  * success and a negative mpsb_status otherwise; it never throws. There is NO CPU fallback:
  * without a CUDA device every compute entry point fails with MPSB_ERR_CUDA.
  *
+ * Environment switches read by the library (diagnostics and tests; none is needed in normal use):
+ *   MPSB_MAX_NEIGHBORS=<K>       neighbour-list / PPE row capacity (default 64 in 2-D, 384 in 3-D)
+ *   MPSB_NO_CLUSTER_SOLVE=1      never use the small-system cluster solve (csrc/k_pcg_cluster.cu)
+ *   MPSB_NO_STEP_GRAPH=1         issue the step's launches directly instead of replaying a CUDA graph
+ *   MPSB_FORCE_WIDE_COLUMNS=1    stream int32 PPE columns even when 16-bit offsets fit
+ *   MPSB_CG_ITERATION_CAP=<n>    stop the solve after n iterations (profiling a bounded solve)
+ * and by the host mirror (mps_b200/host): MPSB_DEVICE=<ordinal>, MPSB_CSV_FLOAT=gcc5.
+ *
  * Particle arrays are SoA, indexed by particle id (the reference assumes id == index,
  * src/mps.cpp:599-617, src/bucket.cpp:36-50). Vectors are packed xyz (3 doubles per particle).
  */

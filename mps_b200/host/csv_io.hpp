@@ -4,6 +4,7 @@
 // single_include/csv.hpp:6641-6681: std::to_string under clang, a 5-decimal digit loop under gcc).
 #pragma once
 
+#include <charconv>
 #include <cmath>
 #include <cstdio>
 #include <string>
@@ -46,10 +47,10 @@ enum class FloatStyle {
 };
 
 inline std::string formatFloat(double value, FloatStyle style) {
-    if (style == FloatStyle::Fixed6) {
-        char buf[64];
-        std::snprintf(buf, sizeof buf, "%f", value);
-        return buf;
+    if (style == FloatStyle::Fixed6) { // std::to_chars(fixed, 6) is specified to print what "%f" prints, several times faster
+        char buf[400];
+        auto r = std::to_chars(buf, buf + sizeof buf, value, std::chars_format::fixed, 6);
+        return std::string(buf, r.ptr);
     }
     // digit-by-digit, integral and fractional part apart; each digit = trunc(fmod(part, 10^k) / 10^(k-1))
     auto p10 = [](int k) {

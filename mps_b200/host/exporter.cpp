@@ -2,22 +2,50 @@
 
 #include "log.hpp"
 
+#include <algorithm>
+#include <charconv>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <thread>
+#include <vector>
 
 namespace {
 // operator<<(ostream, double) with default flags == "%g" with precision 6 (reference src/exporter.cpp:83-131)
-inline void appendG(std::string& s, double v) {
+inline void appendG(std::string& s, double v) { // std::to_chars(general, 6) == "%g"
     char buf[40];
-    int n = std::snprintf(buf, sizeof buf, "%g", v);
-    s.append(buf, (std::size_t) n);
+    auto r = std::to_chars(buf, buf + sizeof buf, v, std::chars_format::general, 6);
+    s.append(buf, (std::size_t) (r.ptr - buf));
 }
 inline void appendInt(std::string& s, long long v) {
     char buf[24];
-    int n = std::snprintf(buf, sizeof buf, "%lld", v);
-    s.append(buf, (std::size_t) n);
+    auto r = std::to_chars(buf, buf + sizeof buf, v);
+    s.append(buf, (std::size_t) (r.ptr - buf));
+}
+// Formats [0, n) in parallel: `body(out, begin, end)` appends the text of particles [begin, end) to `out`; the
+// pieces are concatenated in index order, so the file is the one a serial loop would write.
+template <class Body>
+void appendParallel(std::string& out, std::size_t n, Body body) {
+    const std::size_t minChunk = 1u << 16;
+    std::size_t workers = std::min<std::size_t>(std::max(1u, std::thread::hardware_concurrency()), (n + minChunk - 1) / minChunk);
+    if (workers <= 1) {
+        body(out, (std::size_t) 0, n);
+        return;
+    }
+    std::vector<std::string> piece(workers);
+    std::vector<std::thread> pool;
+    const std::size_t per = (n + workers - 1) / workers;
+    for (std::size_t w = 0; w < workers; w++)
+        pool.emplace_back([&, w] {
+            const std::size_t b = w * per, e = std::min(n, b + per);
+            if (b < e) {
+                piece[w].reserve((e - b) * 96);
+                body(piece[w], b, e);
+            }
+        });
+    for (auto& t : pool) t.join();
+    for (auto& p : piece) out += p;
 }
 bool writeAll(const std::filesystem::path& path, const std::string& data) {
     std::FILE* f = std::fopen(path.string().c_str(), "wb");
@@ -41,19 +69,23 @@ void Exporter::toCsv(const std::filesystem::path& outFilePath, const std::vector
     appendInt(out, (long long) particles.size()); // counts ghosts too, as the reference (SURVEY B-7)
     out += "\nID,Type,Position.x (m),Position.y (m),Position.z (m),Velocity.x (m/s),Velocity.y (m/s),Velocity.z (m/s),"
            "Pressure (Pa),Number Density Ratio\n";
-    for (const Particle& pi : particles) {
-        if (pi.type == ParticleType::Ghost) continue;
-        appendInt(out, pi.id);
-        out += ',';
-        appendInt(out, static_cast<int>(pi.type));
-        const double v[8] = {pi.position.x(), pi.position.y(), pi.position.z(), pi.velocity.x(), pi.velocity.y(), pi.velocity.z(),
-                             pi.pressure, pi.numberDensityRatio};
-        for (double x : v) {
-            out += ',';
-            out += csv_io::formatFloat(x, floatStyle);
+    const csv_io::FloatStyle style = floatStyle;
+    appendParallel(out, particles.size(), [&particles, style](std::string& o, std::size_t b, std::size_t e) {
+        for (std::size_t i = b; i < e; i++) {
+            const Particle& pi = particles[i];
+            if (pi.type == ParticleType::Ghost) continue;
+            appendInt(o, pi.id);
+            o += ',';
+            appendInt(o, static_cast<int>(pi.type));
+            const double v[8] = {pi.position.x(), pi.position.y(), pi.position.z(), pi.velocity.x(), pi.velocity.y(), pi.velocity.z(),
+                                 pi.pressure, pi.numberDensityRatio};
+            for (double x : v) {
+                o += ',';
+                o += csv_io::formatFloat(x, style);
+            }
+            o += '\n';
         }
-        out += '\n';
-    }
+    });
     if (!writeAll(outFilePath, out)) mpslog::error("Could not open target csv file: " + outFilePath.string());
 }
 
@@ -83,57 +115,79 @@ void Exporter::toVtu(const std::filesystem::path& outFilePath, const std::vector
     appendInt(out, (long long) n);
     out += "'>\n<Points>\n";
     out += "<DataArray NumberOfComponents='3' type='Float64' Name='position' format='ascii'>\n";
-    for (const Particle& pi : particles) { // ghosts stay in the VTU (SURVEY B-7)
-        appendG(out, pi.position.x());
-        out += ' ';
-        appendG(out, pi.position.y());
-        out += ' ';
-        appendG(out, pi.position.z());
-        out += '\n';
-    }
+    appendParallel(out, n, [&particles](std::string& o, std::size_t b, std::size_t e) {
+        for (std::size_t i = b; i < e; i++) {
+            const Particle& pi = particles[i];
+            appendG(o, pi.position.x()); // ghosts stay in the VTU (SURVEY B-7)
+            o += ' ';
+            appendG(o, pi.position.y());
+            o += ' ';
+            appendG(o, pi.position.z());
+            o += '\n';
+        }
+    });
     out += "</DataArray>\n</Points>\n<PointData>\n";
     arrayBegin("1", "Int32", "Type");
-    for (const Particle& pi : particles) {
-        appendInt(out, static_cast<int>(pi.type));
-        out += '\n';
-    }
+    appendParallel(out, n, [&particles](std::string& o, std::size_t b, std::size_t e) {
+        for (std::size_t i = b; i < e; i++) {
+            const Particle& pi = particles[i];
+            appendInt(o, static_cast<int>(pi.type));
+            o += '\n';
+        }
+    });
     out += "</DataArray>\n";
     arrayBegin("3", "Float64", "Velocity");
-    for (const Particle& pi : particles) { // z component written as a literal zero, as the reference
-        appendG(out, pi.velocity.x());
-        out += ' ';
-        appendG(out, pi.velocity.y());
-        out += " 0\n";
-    }
+    appendParallel(out, n, [&particles](std::string& o, std::size_t b, std::size_t e) {
+        for (std::size_t i = b; i < e; i++) {
+            const Particle& pi = particles[i];
+            appendG(o, pi.velocity.x()); // z component written as a literal zero, as the reference
+            o += ' ';
+            appendG(o, pi.velocity.y());
+            o += " 0\n";
+        }
+    });
     out += "</DataArray>\n";
     arrayBegin("1", "Float64", "Pressure");
-    for (const Particle& pi : particles) {
-        appendG(out, pi.pressure);
-        out += '\n';
-    }
+    appendParallel(out, n, [&particles](std::string& o, std::size_t b, std::size_t e) {
+        for (std::size_t i = b; i < e; i++) {
+            const Particle& pi = particles[i];
+            appendG(o, pi.pressure);
+            o += '\n';
+        }
+    });
     out += "</DataArray>\n";
     arrayBegin("1", "Float64", "Number Density Ratio");
-    for (const Particle& pi : particles) {
-        appendG(out, pi.numberDensityRatio);
-        out += '\n';
-    }
+    appendParallel(out, n, [&particles](std::string& o, std::size_t b, std::size_t e) {
+        for (std::size_t i = b; i < e; i++) {
+            const Particle& pi = particles[i];
+            appendG(o, pi.numberDensityRatio);
+            o += '\n';
+        }
+    });
     out += "</DataArray>\n";
     arrayBegin("1", "Int32", "Boundary Condition");
-    for (const Particle& pi : particles) {
-        appendInt(out, static_cast<int>(pi.boundaryCondition));
-        out += '\n';
-    }
+    appendParallel(out, n, [&particles](std::string& o, std::size_t b, std::size_t e) {
+        for (std::size_t i = b; i < e; i++) {
+            const Particle& pi = particles[i];
+            appendInt(o, static_cast<int>(pi.boundaryCondition));
+            o += '\n';
+        }
+    });
     out += "</DataArray>\n</PointData>\n<Cells>\n";
     out += "<DataArray type='Int32' Name='connectivity' format='ascii'>\n";
-    for (std::size_t i = 0; i < n; i++) {
-        appendInt(out, (long long) i);
-        out += '\n';
-    }
+    appendParallel(out, n, [](std::string& o, std::size_t b, std::size_t e) {
+        for (std::size_t i = b; i < e; i++) {
+            appendInt(o, (long long) i);
+            o += '\n';
+        }
+    });
     out += "</DataArray>\n<DataArray type='Int32' Name='offsets' format='ascii'>\n";
-    for (std::size_t i = 0; i < n; i++) {
-        appendInt(out, (long long) i + 1);
-        out += '\n';
-    }
+    appendParallel(out, n, [](std::string& o, std::size_t b, std::size_t e) {
+        for (std::size_t i = b; i < e; i++) {
+            appendInt(o, (long long) i + 1);
+            o += '\n';
+        }
+    });
     out += "</DataArray>\n<DataArray type='UInt8' Name='types' format='ascii'>\n";
     for (std::size_t i = 0; i < n; i++) out += "1\n";
     out += "</DataArray>\n</Cells>\n</Piece>\n</UnstructuredGrid>\n</VTKFile>\n";

@@ -2,9 +2,12 @@
 //   host_selftest settings <settings.yml>            parsed Settings + RefValues, one "key value" per line (%.17g)
 //   host_selftest reexport <settings.yml> <out dir>  input CSV -> particles -> out/particles.csv, out/particles.vtu
 //   host_selftest float <style> <value>...           spelling of doubles (style: fixed6 | gcc5)
+//   host_selftest exportbench <n> <out dir>          time Exporter::toCsv / toVtu on n synthetic particles (SURVEY f-1)
 #include "exporter.hpp"
 #include "mps.hpp"
 
+#include <chrono>
+#include <cstdint>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -21,6 +24,29 @@ int main(int argc, char** argv) {
     if (mode == "float") {
         auto style = std::strcmp(argv[2], "gcc5") == 0 ? csv_io::FloatStyle::Trunc5Gcc : csv_io::FloatStyle::Fixed6;
         for (int i = 3; i < argc; i++) std::printf("%s\n", csv_io::formatFloat(std::strtod(argv[i], nullptr), style).c_str());
+        return 0;
+    }
+    if (mode == "exportbench" && argc >= 4) {
+        const long n = std::atol(argv[2]);
+        std::vector<Particle> ps;
+        ps.reserve((std::size_t) n);
+        for (long i = 0; i < n; i++) {
+            const double x = 1e-4 * (double) (i % 2832), y = 1e-4 * (double) (i / 2832);
+            ps.push_back(Particle((int) i, ParticleType::Fluid, Eigen::Vector3d(x, y, 0.0), Eigen::Vector3d(0.1 * x, -0.2 * y, 0.0), 1000.0));
+            ps.back().pressure           = 9800.0 * (0.2 - y);
+            ps.back().numberDensityRatio = 0.97 + 1e-9 * (double) i;
+        }
+        Exporter e;
+        const std::filesystem::path dir(argv[3]);
+        auto t0 = std::chrono::steady_clock::now();
+        e.toCsv(dir / "bench.csv", ps, 1.25);
+        auto t1 = std::chrono::steady_clock::now();
+        e.toVtu(dir / "bench.vtu", ps, 1.25);
+        auto t2 = std::chrono::steady_clock::now();
+        const double csvS = std::chrono::duration<double>(t1 - t0).count(), vtuS = std::chrono::duration<double>(t2 - t1).count();
+        std::printf("particles %ld csv_s %.3f csv_bytes %ju vtu_s %.3f vtu_bytes %ju\n", n, csvS,
+                    (std::uintmax_t) std::filesystem::file_size(dir / "bench.csv"), vtuS,
+                    (std::uintmax_t) std::filesystem::file_size(dir / "bench.vtu"));
         return 0;
     }
     MPS mps{std::filesystem::path(argv[2])};
