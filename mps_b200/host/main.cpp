@@ -1,6 +1,6 @@
 // main.cpp — the reference's CLI (reference src/main.cpp:12-42): `mps -s|--setting <settings.yml>`.
 // Own argument handling (the reference uses argparse). Extra, optional: --max-steps N, --quiet,
-// --plain-report (only the reference's 12 report columns).
+// --plain-report (only the reference's 12 report columns), --state-in / --state-out FILE (binary checkpoints).
 #include "simulation.hpp"
 
 #include <cstdlib>
@@ -20,12 +20,16 @@ int main(int argc, char** argv) {
             setting = a.substr(10);
         } else if (a == "--max-steps" && i + 1 < argc) {
             simulation.maxSteps = std::atoi(argv[++i]);
+        } else if (a == "--state-in" && i + 1 < argc) {
+            simulation.stateIn = argv[++i];
+        } else if (a == "--state-out" && i + 1 < argc) {
+            simulation.stateOut = argv[++i];
         } else if (a == "--quiet") {
             simulation.quiet = true;
         } else if (a == "--plain-report") {
             simulation.extendedReport = false;
         } else if (a == "-h" || a == "--help") {
-            std::cout << "Usage: mps [-h] --setting VAR [--max-steps N] [--quiet] [--plain-report]\n\n"
+            std::cout << "Usage: mps [-h] --setting VAR [--max-steps N] [--state-in FILE] [--state-out FILE] [--quiet] [--plain-report]\n\n"
                          "  -s, --setting  path to YAML file for settings. [required]\n";
             return 0;
         } else {

@@ -3,6 +3,7 @@
 #include "../../include/mps_b200.h"
 #include "csv_io.hpp"
 #include "log.hpp"
+#include "state_io.hpp"
 
 #include <algorithm>
 #include <cstdlib>
@@ -88,7 +89,7 @@ double MPS::importInitialCondition() {
     return initialTime;
 }
 
-void MPS::createDeviceState() {
+void MPS::createDeviceState(bool restoreDerived) {
     mpsb_settings s;
     std::memset(&s, 0, sizeof s);
     s.dim                      = (int) settings.dim;
@@ -144,7 +145,36 @@ void MPS::createDeviceState() {
     // setNumberDensity at the beginning, as reference loadInitialState (src/mps.cpp:104-106)
     rc = mpsb_run_phase(h, MPSB_PH_NUMBER_DENSITY, nullptr);
     if (rc != MPSB_OK) fail("initial setNumberDensity", rc);
+    if (restoreDerived) { // checkpoint: put back what the interrupted run held instead of the freshly derived values
+        std::vector<std::int32_t> bc(n);
+        std::vector<double> p(n), ratio(n);
+        for (std::size_t i = 0; i < n; i++) {
+            bc[i]    = static_cast<std::int32_t>(particles[i].boundaryCondition);
+            p[i]     = particles[i].pressure;
+            ratio[i] = particles[i].numberDensityRatio;
+        }
+        mpsb_fields f;
+        std::memset(&f, 0, sizeof f);
+        f.pressure = p.data(); f.number_density_ratio = ratio.data(); f.boundary_condition = bc.data();
+        rc = mpsb_upload(h, MPSB_F_PRESSURE | MPSB_F_NUMBER_DENSITY_RATIO | MPSB_F_BOUNDARY_CONDITION, &f);
+        if (rc != MPSB_OK) fail("mpsb_upload (checkpoint)", rc);
+    }
     downloadParticles();
+}
+
+double MPS::loadInitialStateFromFile(const std::filesystem::path& statePath) {
+    double time = 0.0;
+    if (!state_io::read(statePath, time, particles, settings.density)) {
+        mpslog::error("Could not read the state file: " + statePath.string());
+        std::exit(EXIT_FAILURE);
+    }
+    createDeviceState(true);
+    return time;
+}
+
+bool MPS::saveState(const std::filesystem::path& statePath, double time) {
+    downloadParticles();
+    return state_io::write(statePath, time, particles);
 }
 
 double MPS::loadInitialState() {

@@ -58,6 +58,11 @@ public:
         double time, std::int64_t n, const std::int32_t* type, const double* position3, const double* velocity3
     );
     double loadParticlesOnly() { return importInitialCondition(); } // CSV -> particles, no device (host tests, converters)
+    // Binary state files (state_io.hpp): full-precision checkpoints. Loading one restores type, position,
+    // velocity and the derived fields a following step can depend on (pressure, number-density ratio, flags),
+    // so save + load + continue equals an uninterrupted run bit for bit. Returns the file's time.
+    double loadInitialStateFromFile(const std::filesystem::path& statePath);
+    bool saveState(const std::filesystem::path& statePath, double time); // downloads first
     int device = 0; // CUDA device ordinal used by loadInitialState (MPSB_DEVICE overrides)
 
     const RefValues& refValuesPressure() const { return refValues.pressure; }
@@ -76,7 +81,7 @@ private:
     std::shared_ptr<mpsb_handle> handle;
 
     double importInitialCondition(); // reference src/mps.cpp:38-94
-    void createDeviceState();
+    void createDeviceState(bool restoreDerived = false);
     void reportEvents(const mpsb_step_stats& stats);
     [[noreturn]] void fail(const char* what, int status);
 };

@@ -38,7 +38,7 @@ void Simulation::run(const fs::path& inputYamlPath) {
     prepareLogFile();
 
     mps  = MPS(inputYamlPath);
-    time = mps.loadInitialState();
+    time = stateIn.empty() ? mps.loadInitialState() : mps.loadInitialStateFromFile(stateIn);
     exportParticles(mps.particles);
 
     mpslog::info("START SIMULATION");
@@ -60,6 +60,7 @@ void Simulation::run(const fs::path& inputYamlPath) {
         timeStep++;
     }
     simulationEndTime = system_clock::now();
+    if (!stateOut.empty() && !mps.saveState(stateOut, time)) mpslog::error("Could not write the state file: " + stateOut.string());
     endSimulation();
 }
 

@@ -20,6 +20,7 @@ public:
     bool extendedReport = true;
     bool quiet          = false;
     int maxSteps        = 0;
+    std::filesystem::path stateIn, stateOut; // binary checkpoint to start from / to write at the end (state_io.hpp)
 
 private:
     MPS mps;

@@ -13,13 +13,14 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 HOST = os.path.join(ROOT, "mps_b200", "host")
 SELFTEST = os.path.join(HOST, "host_selftest")
 MPS_EXE = os.path.join(HOST, "mps")
+GEN_EXE = os.path.join(HOST, "mps_generate")
 REF_EXE = os.path.join(ROOT, "oracle", "_ref", "main.exe")
 CASES = ["dambreak", "dambreak_fine", "hydrostatic", "dambreak_fine_higher_order", "dambreak_fine_original"]
 
 
 @pytest.fixture(scope="module", autouse=True)
 def _built():
-    if not (os.path.exists(SELFTEST) and os.path.exists(MPS_EXE)):
+    if not (os.path.exists(SELFTEST) and os.path.exists(MPS_EXE) and os.path.exists(GEN_EXE)):
         from mps_b200 import build as B
 
         B.build_library()
@@ -155,3 +156,72 @@ def test_cli_outputs_match_reference_binary(case, finish, interval, tmp_path):
     for a, b in zip(rep_a[1:], rep_b[1:]):
         for col in (0, 1, 2, 3, 4, 10, 11):  # step, dt, times, finish, files written, Courant
             assert a[col] == b[col], (col, a, b)
+
+
+def read_state(path):
+    """Binary state of mps_b200/host/state_io.hpp -> dict of arrays."""
+    import numpy as np
+
+    raw = open(path, "rb").read()
+    assert raw[:8] == b"MPSBST1\x00"
+    n = int(np.frombuffer(raw, np.int64, 1, 8)[0])
+    out = {"time": float(np.frombuffer(raw, np.float64, 1, 16)[0]), "n": n}
+    off = 24
+    for name, dt, cnt in (("type", np.int32, n), ("boundary_condition", np.int32, n), ("position", np.float64, 3 * n),
+                          ("velocity", np.float64, 3 * n), ("pressure", np.float64, n), ("number_density_ratio", np.float64, n)):
+        out[name] = np.frombuffer(raw, dt, cnt, off)
+        off += cnt * np.dtype(dt).itemsize
+    assert off == len(raw)
+    out["position"] = out["position"].reshape(n, 3)
+    out["velocity"] = out["velocity"].reshape(n, 3)
+    return out
+
+
+@pytest.mark.parametrize("case,nx", [("dambreak", 0), ("dambreak_fine", 0), ("hydrostatic", 0), ("dambreak_fine", 400)])
+def test_cpp_generator_equals_python_generator_bitwise(case, nx, tmp_path):
+    """host/generator.hpp (C++) against mps_b200.cases.generate_lattice (the generator the golden fixtures and the
+    bench use): same ids, types and full-precision positions; for the shipped sizes also the reference's input.csv."""
+    import numpy as np
+
+    out = tmp_path / "s.bin"
+    args = [GEN_EXE, "--case", case, "--state", str(out), "--csv", str(tmp_path / "input.csv")]
+    if nx:
+        args += ["--nx", str(nx)]
+    r = _run(*args)
+    assert r.returncode == 0, r.stderr
+    st = read_state(out)
+    if nx:
+        S, t, p, v = C.scaled_dambreak(nx, base=case)
+    else:
+        g = C.GEOMETRIES[case]
+        t, p = C.generate_lattice(g["l0"], g["domain_x"], g["domain_y"], g["fluid_x"], g["fluid_y"])
+        assert open(tmp_path / "input.csv", "rb").read() == open(C.case_paths(case)[1], "rb").read()
+    assert st["n"] == len(t) and np.array_equal(st["type"], t) and np.array_equal(st["position"], p)
+    assert not st["velocity"].any() and st["time"] == 0.0
+
+
+@pytest.mark.gpu
+def test_checkpoint_restart_is_bitwise_an_uninterrupted_run(tmp_path):
+    """mps --state-out after k steps, then --state-in for m more steps == k + m steps straight: every field of the
+    final binary states identical (higher-order source term on, so the saved ratio and flags matter)."""
+    import numpy as np
+
+    S = C.load_settings(C.case_paths("dambreak_fine_higher_order")[0])
+    dt = S.dt
+
+    def run(tag, finish, state_in=None):
+        d = tmp_path / tag
+        d.mkdir()
+        yml = C.write_settings_yaml(S, str(d / "settings.yml"), finish_time=finish, output_interval=1.0)
+        out = d / "final.bin"
+        cmd = [MPS_EXE, "-s", yml, "--quiet", "--state-out", str(out)] + (["--state-in", str(state_in)] if state_in else [])
+        r = _run(*cmd)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+        return read_state(out)
+
+    straight = run("straight", 30.5 * dt)
+    first = run("first", 12.5 * dt)
+    second = run("second", 30.5 * dt, tmp_path / "first" / "final.bin")
+    assert abs(first["time"] - 12 * dt) < 1e-12 and abs(second["time"] - straight["time"]) < 1e-15
+    for k in ("type", "boundary_condition", "position", "velocity", "pressure", "number_density_ratio"):
+        assert np.array_equal(second[k], straight[k]), k
