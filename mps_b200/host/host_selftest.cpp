@@ -2,9 +2,11 @@
 //   host_selftest settings <settings.yml>            parsed Settings + RefValues, one "key value" per line (%.17g)
 //   host_selftest reexport <settings.yml> <out dir>  input CSV -> particles -> out/particles.csv, out/particles.vtu
 //   host_selftest float <style> <value>...           spelling of doubles (style: fixed6 | gcc5)
+//   host_selftest rendezvous x                       RANK/WORLD_SIZE/MASTER_* from the environment: share a 128-byte id, print its sum
 //   host_selftest exportbench <n> <out dir>          time Exporter::toCsv / toVtu on n synthetic particles (SURVEY f-1)
 #include "exporter.hpp"
 #include "mps.hpp"
+#include "rendezvous.hpp"
 
 #include <chrono>
 #include <cstdint>
@@ -24,6 +26,20 @@ int main(int argc, char** argv) {
     if (mode == "float") {
         auto style = std::strcmp(argv[2], "gcc5") == 0 ? csv_io::FloatStyle::Trunc5Gcc : csv_io::FloatStyle::Fixed6;
         for (int i = 3; i < argc; i++) std::printf("%s\n", csv_io::formatFloat(std::strtod(argv[i], nullptr), style).c_str());
+        return 0;
+    }
+    if (mode == "rendezvous") {
+        const rendezvous::Env env = rendezvous::fromEnvironment();
+        unsigned char id[128] = {0};
+        if (env.rank == 0)
+            for (int i = 0; i < 128; i++) id[i] = (unsigned char) (i * 7 + 3);
+        if (!rendezvous::shareUniqueId(env, id)) {
+            std::printf("rank %d rendezvous failed\n", env.rank);
+            return 1;
+        }
+        unsigned sum = 0;
+        for (int i = 0; i < 128; i++) sum += id[i] * (unsigned) (i + 1);
+        std::printf("rank %d of %d sum %u\n", env.rank, env.world, sum);
         return 0;
     }
     if (mode == "exportbench" && argc >= 4) {

@@ -3,6 +3,7 @@
 #include "../../include/mps_b200.h"
 #include "csv_io.hpp"
 #include "log.hpp"
+#include "rendezvous.hpp"
 #include "state_io.hpp"
 
 #include <algorithm>
@@ -133,6 +134,10 @@ void MPS::createDeviceState(bool restoreDerived) {
             vel[3 * i + k] = pi.velocity[k];
         }
     }
+    const rendezvous::Env env = rendezvous::fromEnvironment();
+    rank      = env.rank;
+    worldSize = env.world;
+    if (worldSize > 1) device = env.localRank;
     if (const char* d = std::getenv("MPSB_DEVICE")) device = std::atoi(d);
     mpsb_handle* h = nullptr;
     int rc         = mpsb_create(&s, (std::int64_t) n, type.data(), pos.data(), vel.data(), device, &h);
@@ -142,6 +147,19 @@ void MPS::createDeviceState(bool restoreDerived) {
         std::exit(EXIT_FAILURE);
     }
     handle = std::shared_ptr<mpsb_handle>(h, [](mpsb_handle* p) { mpsb_destroy(p); });
+    if (worldSize > 1) {
+        unsigned char id[128] = {0};
+        if (rank == 0 && mpsb_comm_unique_id(id) != MPSB_OK) {
+            mpslog::error("mpsb_comm_unique_id failed: NCCL (libnccl.so.2) is required for multi-GPU runs");
+            std::exit(EXIT_FAILURE);
+        }
+        if (!rendezvous::shareUniqueId(env, id)) {
+            mpslog::error("Multi-GPU rendezvous failed (MASTER_ADDR=" + env.addr + ", port " + std::to_string(env.port + 1) + ")");
+            std::exit(EXIT_FAILURE);
+        }
+        rc = mpsb_attach_comm(h, rank, worldSize, id);
+        if (rc != MPSB_OK) fail("mpsb_attach_comm", rc);
+    }
     // setNumberDensity at the beginning, as reference loadInitialState (src/mps.cpp:104-106)
     rc = mpsb_run_phase(h, MPSB_PH_NUMBER_DENSITY, nullptr);
     if (rc != MPSB_OK) fail("initial setNumberDensity", rc);

@@ -64,6 +64,9 @@ public:
     double loadInitialStateFromFile(const std::filesystem::path& statePath);
     bool saveState(const std::filesystem::path& statePath, double time); // downloads first
     int device = 0; // CUDA device ordinal used by loadInitialState (MPSB_DEVICE overrides)
+    // Multi-GPU: one process per GPU. With WORLD_SIZE > 1 in the environment (rendezvous.hpp) the ranks split the
+    // PPE solve; every rank holds the whole particle set and returns identical results.
+    int rank = 0, worldSize = 1;
 
     const RefValues& refValuesPressure() const { return refValues.pressure; }
     const RefValues& refValuesViscosity() const { return refValues.viscosity; }

@@ -3,6 +3,7 @@
 #include "csv_io.hpp"
 #include "exporter.hpp"
 #include "log.hpp"
+#include "rendezvous.hpp"
 
 #include <cmath>
 #include <cstdio>
@@ -34,12 +35,19 @@ std::string secondsOfMinute(long long ms) {
 } // namespace
 
 void Simulation::run(const fs::path& inputYamlPath) {
-    createResultDirectory(inputYamlPath);
-    prepareLogFile();
+    // multi-GPU (one process per GPU): every rank steps the same simulation; only rank 0 writes files and logs
+    writer = rendezvous::fromEnvironment().rank == 0;
+    if (writer) {
+        createResultDirectory(inputYamlPath);
+        prepareLogFile();
+    } else {
+        mpslog::Logger::get().setConsole(false);
+        quiet = true;
+    }
 
     mps  = MPS(inputYamlPath);
     time = stateIn.empty() ? mps.loadInitialState() : mps.loadInitialStateFromFile(stateIn);
-    exportParticles(mps.particles);
+    if (writer) exportParticles(mps.particles);
 
     mpslog::info("START SIMULATION");
     simulationStartTime = system_clock::now();
@@ -53,14 +61,14 @@ void Simulation::run(const fs::path& inputYamlPath) {
         time += mps.settings.dt;
         const bool exportNow = isTimeToExport();
         double courantNumber = mps.stepForward(exportNow);
-        if (exportNow) exportParticles(mps.particles);
+        if (exportNow && writer) exportParticles(mps.particles);
 
         auto timeStepEndTime = system_clock::now();
-        timeStepReport(timeStepStartTime, timeStepEndTime, courantNumber, mps.debugLogCount > initialDebugLogCount);
+        if (writer) timeStepReport(timeStepStartTime, timeStepEndTime, courantNumber, mps.debugLogCount > initialDebugLogCount);
         timeStep++;
     }
     simulationEndTime = system_clock::now();
-    if (!stateOut.empty() && !mps.saveState(stateOut, time)) mpslog::error("Could not write the state file: " + stateOut.string());
+    if (writer && !stateOut.empty() && !mps.saveState(stateOut, time)) mpslog::error("Could not write the state file: " + stateOut.string());
     endSimulation();
 }
 

@@ -24,6 +24,7 @@ public:
 
 private:
     MPS mps;
+    bool writer = true; // rank 0 of a multi-GPU run (or the only process)
 
     int timeStep = 0;
     double time  = 0.0;

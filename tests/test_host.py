@@ -225,3 +225,16 @@ def test_checkpoint_restart_is_bitwise_an_uninterrupted_run(tmp_path):
     assert abs(first["time"] - 12 * dt) < 1e-12 and abs(second["time"] - straight["time"]) < 1e-15
     for k in ("type", "boundary_condition", "position", "velocity", "pressure", "number_density_ratio"):
         assert np.array_equal(second[k], straight[k]), k
+
+
+def test_cpp_rendezvous_shares_the_id_between_three_processes():
+    """host/rendezvous.hpp: rank 0 serves a 128-byte id over TCP on MASTER_PORT + 1, the others fetch it."""
+    port = 30100 + os.getpid() % 500
+    procs = []
+    for rank in (1, 2, 0):  # clients first: they must retry until the server is up
+        env = dict(os.environ, RANK=str(rank), WORLD_SIZE="3", LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+        procs.append(subprocess.Popen([SELFTEST, "rendezvous", "x"], stdout=subprocess.PIPE, text=True, env=env))
+    outs = [p.communicate(timeout=120)[0] for p in procs]
+    assert all(p.returncode == 0 for p in procs), outs
+    sums = {o.split()[-1] for o in outs}
+    assert len(sums) == 1 and sums != {"0"}, outs

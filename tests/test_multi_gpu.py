@@ -85,3 +85,38 @@ def test_split_solve_matches_single_gpu(case, steps):
     assert r.returncode == 0 and lines, r.stdout[-2000:] + r.stderr[-2000:]
     rep = json.loads(lines[-1])
     assert rep["ok"] and rep["ranks_bit_identical"] and rep["flags_equal"], rep
+
+
+@pytest.mark.gpu
+def test_cpp_host_runs_one_process_per_gpu(tmp_path):
+    """./mps launched as two processes (RANK/WORLD_SIZE/LOCAL_RANK/MASTER_* in the environment, C++ rendezvous, no
+    Python): rank 0's final checkpoint against a single-process run of the same case — flags identical, fields
+    within 1e-10 (only the reduction order of the split solve differs)."""
+    if _gpu_count() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    import numpy as np
+
+    from mps_b200 import cases as C
+    from tests.test_host import MPS_EXE, read_state
+
+    S = C.load_settings(C.case_paths("dambreak_fine")[0])
+
+    def launch(tag, world):
+        d = tmp_path / tag
+        d.mkdir()
+        yml = C.write_settings_yaml(S, str(d / "settings.yml"), finish_time=8.5 * S.dt, output_interval=1.0)
+        procs = []
+        for rank in range(world):
+            env = dict(os.environ, RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1",
+                       MASTER_PORT=str(29900 + os.getpid() % 90))
+            procs.append(subprocess.Popen([MPS_EXE, "-s", yml, "--quiet", "--state-out", str(d / "final.bin")], cwd=ROOT,
+                                          stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env))
+        outs = [p.communicate(timeout=300)[0] for p in procs]
+        assert all(p.returncode == 0 for p in procs), outs
+        return read_state(d / "final.bin")
+
+    one, two = launch("one", 1), launch("two", 2)
+    assert np.array_equal(one["type"], two["type"]) and np.array_equal(one["boundary_condition"], two["boundary_condition"])
+    for k in ("position", "velocity", "pressure"):
+        scale = max(float(np.abs(one[k]).max()), 1e-300)
+        assert float(np.abs(one[k] - two[k]).max()) / scale <= 1e-10, k
