@@ -18,8 +18,15 @@ constexpr int RADIX        = 256;
 // Cell key from the HOME position, by particle id. ix = (int)((x - xmin)/len) + 1 with a true
 // division and C truncation (src/bucket.cpp:40-43). A non-ghost particle whose cell would make the
 // reference's 27-cell scan index outside its arrays raises the out-of-grid flag (SURVEY B-8).
+// It also clears the cell ranges and the active count of the previous build (they are rewritten by
+// cell_range_kernel, several kernels later), which saves three memset nodes per build.
 __global__ void key_kernel(Params P) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
+    for (int c = i; c < P.numCells; c += gridDim.x * blockDim.x) {
+        P.cell_start[c] = 0;
+        P.cell_end[c]   = 0;
+    }
+    if (i == 0) *P.n_active = 0;
     if (i >= P.N) return;
     unsigned key = MPSB_GHOST_KEY;
     if (P.H.type[i] != MPSB_GHOST) {
@@ -251,9 +258,6 @@ void mpsb_launch_cell_build(mpsb_handle* h) {
         unsigned* tk = P.key; P.key = P.key_alt; P.key_alt = tk;
         int* tv = P.val; P.val = P.val_alt; P.val_alt = tv;
     }
-    cudaMemsetAsync(P.cell_start, 0, sizeof(int) * (size_t) P.numCells, h->stream);
-    cudaMemsetAsync(P.cell_end, 0, sizeof(int) * (size_t) P.numCells, h->stream);
-    cudaMemsetAsync(P.n_active, 0, sizeof(int), h->stream);
     MPSB_LAUNCH(h, cell_range_kernel, grid, 256, 0, P);
     MPSB_LAUNCH(h, gather_all_kernel, grid, 256, 0, P, 1);
 }

@@ -92,7 +92,11 @@ __global__ void __launch_bounds__(256) collision_candidates_kernel(Params P) {
 
 __global__ void __launch_bounds__(1024) collision_replay_kernel(Params P) {
     int M = min(*P.cand_count, P.cand_cap);
-    if (threadIdx.x == 0) P.stats->n_collisions = M;
+    __syncthreads(); // every thread has read the count: leave it cleared for the next candidate pass
+    if (threadIdx.x == 0) {
+        *P.cand_count         = 0;
+        P.stats->n_collisions = M;
+    }
     if (M == 0) return;
     // bitonic sort of the keys in global memory (padded with ~0 to a power of two)
     int M2 = 1;
@@ -213,7 +217,6 @@ void mpsb_launch_explicit(mpsb_handle* h) {
 
 void mpsb_launch_collision(mpsb_handle* h) {
     Params& P = h->P;
-    cudaMemsetAsync(P.cand_count, 0, sizeof(int), h->stream);
     MPSB_LAUNCH(h, collision_candidates_kernel, mpsb_div_up(P.N, 256), 256, 0, P);
     MPSB_LAUNCH(h, collision_replay_kernel, 1, 1024, 0, P);
 }
@@ -226,6 +229,6 @@ void mpsb_launch_gradient_move(mpsb_handle* h) {
 
 void mpsb_launch_courant(mpsb_handle* h) {
     Params& P = h->P;
-    cudaMemsetAsync(&P.stats->courant_bits_as_double, 0, sizeof(double), h->stream);
+    if (!h->in_step) cudaMemsetAsync(&P.stats->courant_bits_as_double, 0, sizeof(double), h->stream); // a step clears all stats at once
     MPSB_LAUNCH(h, courant_kernel, mpsb_div_up(P.N, 256), 256, 0, P);
 }

@@ -469,7 +469,10 @@ bulk_g2s(S.val, P.ell_val + off, (unsigned) nsl * 256u, bar);
 // MULTI = false: one GPU, rows [0, n). MULTI = true: this rank's row block; see the file header.
 template <bool MULTI>
 __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_blocks, int iteration_cap) {
-    if (*P.cluster_done) return; // the cluster solve (k_pcg_cluster.cu) already did it; uniform over the grid
+    if (*P.cluster_done) { // the cluster solve (k_pcg_cluster.cu) already did it; uniform over the grid
+        if (blockIdx.x == 0 && threadIdx.x == 0) *P.ell_wide = 0; // consumed: the next assembly starts from "fits"
+        return;
+    }
     if (blockIdx.x == 0 && threadIdx.x == 0) P.stats->t_solve_begin = global_timer_ns();
     cg::grid_group grid = cg::this_grid();
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -727,6 +730,11 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
         P.stats->cg_iterations   = it;
         P.stats->pad[0]          = col16 ? 1 : 0;
         P.stats->pad[1]          = 0;
+        // leave the launch-scoped scratch cleared for the next solve (saves memset nodes): the two slice-queue
+        // counters (no sweep A is running any more) and the column-width flag of the assembly just consumed
+        tickets[0] = 0u;
+        tickets[1] = 0u;
+        *P.ell_wide = 0;
         P.stats->t_solve_end     = global_timer_ns();
         P.stats->rhs_norm2       = rhsNorm2;
         P.stats->cg_rel_residual = rhsNorm2 > 0.0 ? sqrt(residualNorm2 / rhsNorm2) : 0.0;
@@ -760,7 +768,6 @@ void mpsb_launch_pcg(mpsb_handle* h) {
     int grid = want < h->cg_max_blocks ? want : h->cg_max_blocks;
     if (grid < 1) grid = 1;
     int max_blocks = h->cg_max_blocks;
-    cudaMemsetAsync(P.cg_partials + 8 * (size_t) max_blocks, 0, 8, h->stream); // the two slice-queue counters
     if (multi) cudaMemsetAsync(P.L.arrive, 0, 2 * sizeof(unsigned long long), h->stream); // both arrival counters
     int cap = h->cg_iteration_cap;
     void* args[] = {(void*) &P, (void*) &max_blocks, (void*) &cap};

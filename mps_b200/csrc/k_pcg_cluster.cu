@@ -91,6 +91,7 @@ __global__ void __launch_bounds__(CL_THREADS, 1) pcg_cluster_kernel(Params P, in
     __shared__ int meta[CL_MAX][3]; // per rank: does-not-fit flag, window [lo, hi); written through DSMEM
 
     const int C = (int) cluster.num_blocks(), rank = (int) cluster.block_rank();
+    if (rank == 0 && threadIdx.x == 0) *P.cluster_done = 0; // set again at the end if this kernel does the solve
     unsigned long long t_begin;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_begin));
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -360,8 +361,15 @@ int mpsb_pcg_cluster_configure(mpsb_handle* h) {
 // Launches the cluster solve when the case is small enough to have a chance of fitting; returns 1 if launched.
 int mpsb_launch_pcg_cluster(mpsb_handle* h) {
     Params& P = h->P;
-    cudaMemsetAsync(P.cluster_done, 0, sizeof(int), h->stream);
-    if (h->cl_size <= 0 || P.L.world > 1 || P.N > 32767 || h->cl_disable) return 0;
+    // *cluster_done is 0 unless this kernel solved: it clears the flag itself when it starts (no memset node)
+    if (h->cl_size <= 0 || P.L.world > 1 || P.N > 32767 || h->cl_disable) {
+        if (h->cl_launched) { // an earlier solve may have left the flag set (e.g. a communicator attached since)
+            cudaMemsetAsync(P.cluster_done, 0, sizeof(int), h->stream);
+            h->cl_launched = 0;
+        }
+        return 0;
+    }
+    h->cl_launched = 1;
     // cluster size: the smallest power of two whose CTAs are expected to hold their block (rows of the widest
     // lists seen in practice), so tiny systems do not pay a 16-CTA barrier; the kernel itself checks the fit
     const int slices = (P.N + 31) / 32, width = P.s.dim == 2 ? 36 : 128;

@@ -71,8 +71,9 @@ __global__ void __launch_bounds__(256) source_ho_kernel(Params P) {
 // multiple of 4) with entries (column = own row, value = +0.0) so the PCG kernel streams whole slices
 // without per-row trip counts; adding +0.0 * p never changes a finite sum. One warp = one slice, so
 // the grid covers Np rows and no thread exits before the warp-wide maximum.
-__global__ void __launch_bounds__(256) matrix_kernel(Params P) {
+__global__ void __launch_bounds__(256) matrix_kernel(Params P, int force_wide) {
     int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s == 0 && force_wide) *P.ell_wide = 1;
     if (s >= P.Np) return; // Np is a multiple of 32: whole warps leave together
     int m = 0, cmin = s, cmax = s, wide = 0;
     double diag = 0.0;
@@ -213,23 +214,23 @@ __global__ void __launch_bounds__(256) min_pressure_kernel(Params P) {
 void mpsb_launch_flags_source(mpsb_handle* h) {
     Params& P = h->P;
     int grid  = mpsb_div_up(P.N, 256);
-    cudaMemsetAsync(&P.stats->n_inner, 0, 2 * sizeof(int), h->stream); // n_inner, n_surface
+    if (!h->in_step) cudaMemsetAsync(&P.stats->n_inner, 0, 2 * sizeof(int), h->stream); // n_inner, n_surface (a step clears all stats at once)
     MPSB_LAUNCH(h, flags_kernel, grid, 256, 0, P);
     if (P.s.higher_order_source_on) MPSB_LAUNCH(h, source_ho_kernel, grid, 256, 0, P);
 }
 
 void mpsb_launch_matrix(mpsb_handle* h) {
     Params& P = h->P;
-    cudaMemsetAsync(&P.stats->nnz, 0, sizeof(int), h->stream);
+    if (!h->in_step) cudaMemsetAsync(&P.stats->nnz, 0, sizeof(int), h->stream);
     const char* force = getenv("MPSB_FORCE_WIDE_COLUMNS"); // tests: exercise the 32-bit column stream
-    cudaMemsetAsync(P.ell_wide, force && atoi(force) ? 0xFF : 0, sizeof(int), h->stream);
-    MPSB_LAUNCH(h, matrix_kernel, mpsb_div_up(P.Np, 256) , 256, 0, P);
+    // *ell_wide is cleared by the solve that consumed it (pcg_kernel), not by a memset node here
+    MPSB_LAUNCH(h, matrix_kernel, mpsb_div_up(P.Np, 256) , 256, 0, P, force && atoi(force) ? 1 : 0);
 }
 
 void mpsb_launch_dirichlet(mpsb_handle* h) {
     Params& P = h->P;
     int grid  = mpsb_div_up(P.N, 256);
-    cudaMemsetAsync(&P.stats->n_unconnected, 0, sizeof(int), h->stream);
+    if (!h->in_step) cudaMemsetAsync(&P.stats->n_unconnected, 0, sizeof(int), h->stream);
     MPSB_LAUNCH(h, dirichlet_init_kernel, grid, 256, 0, P);
     MPSB_LAUNCH(h, dirichlet_union_kernel, grid, 256, 0, P);
     MPSB_LAUNCH(h, dirichlet_mark_kernel, grid, 256, 0, P);

@@ -322,6 +322,7 @@ static int issue_step(mpsb_handle* h, int want_number_density, bool timed) {
         if (timed) CK(h, cudaEventRecord(E[k], st));                                              \
     } while (0)
     CK(h, cudaMemsetAsync(h->P.stats, 0, sizeof(DevStats), st));
+    h->in_step = 1;
     EV(0);
     build_lists(h);                                  // setNeighbors
     EV(1);
@@ -340,7 +341,10 @@ static int issue_step(mpsb_handle* h, int want_number_density, bool timed) {
     mpsb_launch_dirichlet(h);
     EV(6);
     mpsb_launch_pcg(h);
-    if (h->world > 1 && mpsb_comm_gather_pressure(h)) return h->sticky;
+    if (h->world > 1 && mpsb_comm_gather_pressure(h)) {
+        h->in_step = 0;
+        return h->sticky;
+    }
     EV(7);
     mpsb_launch_pressure_post(h);
     mpsb_launch_gradient_move(h);                    // calcPressureGradient, moveParticlesWithPressureGradient
@@ -355,6 +359,7 @@ static int issue_step(mpsb_handle* h, int want_number_density, bool timed) {
     mpsb_launch_scatter_all(h);
     EV(10);
 #undef EV
+    h->in_step = 0;
     return MPSB_OK;
 }
 

@@ -155,7 +155,9 @@ struct mpsb_handle {
     int cg_iteration_cap;   // diagnostic: stop the solve after this many iterations (0 = Eigen's 2N)
     int num_sms;
     int cl_size, cl_smem;   // cluster solve for small systems (k_pcg_cluster.cu): cluster size (0 = unavailable), dynamic smem
+    int cl_launched;        // the cluster kernel has run on this handle (*cluster_done may be set)
     int cl_disable;         // MPSB_NO_CLUSTER_SOLVE=1: always use the grid kernel (tests)
+    int in_step;            // inside mpsb_step: DevStats was cleared as a whole, launchers skip their own clears
     int graph_enable;       // small cases: replay the step as one CUDA graph (MPSB_NO_STEP_GRAPH=1 disables)
     int n_graphs;
     StepGraph graphs[MPSB_MAX_STEP_GRAPHS];
