@@ -40,16 +40,17 @@ __global__ void __launch_bounds__(256) explicit_kernel(Params P) {
         const double re = P.s.re_viscosity;
         int cnt = P.nbr_count[s];
         double tx = 0.0, ty = 0.0, tz = 0.0;
-        for (int k = 0; k < cnt; k++) {
-            double d = P.nbr_dist[SELL(k, s)];
-            if (d < re) {
-                int j      = P.nbr_idx[SELL(k, s)];
-                double wgt = (re / d) - 1.0;
-                tx += (P.S.u[j] - u) * wgt;
-                ty += (P.S.v[j] - v) * wgt;
-                tz += (P.S.w[j] - w) * wgt;
-            }
-        }
+        struct Vel { double u, v, w; };
+        mpsb_walk_list<8, Vel>(
+            P, s, cnt, [&](int j) { return Vel{P.S.u[j], P.S.v[j], P.S.w[j]}; },
+            [&](int, double d, int, const Vel& q) {
+                if (d < re) {
+                    double wgt = (re / d) - 1.0;
+                    tx += (q.u - u) * wgt;
+                    ty += (q.v - v) * wgt;
+                    tz += (q.w - w) * wgt;
+                }
+            });
         tx *= P.visc_coef; ty *= P.visc_coef; tz *= P.visc_coef;
         double ax = P.s.gravity[0] + tx, ay = P.s.gravity[1] + ty, az = P.s.gravity[2] + tz;
         const double dt = P.s.dt;
@@ -76,18 +77,19 @@ __global__ void __launch_bounds__(256) collision_candidates_kernel(Params P) {
     int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= *P.n_active || P.S.type[s] != MPSB_FLUID) return;
     int cnt = P.nbr_count[s], id = P.S.id[s];
-    for (int k = 0; k < cnt; k++) {
-        double d = P.nbr_dist[SELL(k, s)];
-        if (d < P.s.collision_distance) {
-            int j = P.nbr_idx[SELL(k, s)];
-            if (P.S.type[j] == MPSB_FLUID && P.S.id[j] >= id) continue;
-            int c = atomicAdd(P.cand_count, 1);
-            if (c < P.cand_cap)
-                P.cand[c] = ((unsigned long long) (unsigned) id << 32) | (unsigned) k;
-            else
-                atomicOr(&P.stats->error_flags, 1);
-        }
-    }
+    // candidates are rare: only the distances are batched, the neighbour's type and id are read on a hit
+    mpsb_walk_list<8, MpsbNoRec>(
+        P, s, cnt, [](int) { return MpsbNoRec{}; },
+        [&](int k, double d, int j, const MpsbNoRec&) {
+            if (d < P.s.collision_distance) {
+                if (P.S.type[j] == MPSB_FLUID && P.S.id[j] >= id) return;
+                int c = atomicAdd(P.cand_count, 1);
+                if (c < P.cand_cap)
+                    P.cand[c] = ((unsigned long long) (unsigned) id << 32) | (unsigned) k;
+                else
+                    atomicOr(&P.stats->error_flags, 1);
+            }
+        });
 }
 
 __global__ void __launch_bounds__(1024) collision_replay_kernel(Params P) {
@@ -157,17 +159,18 @@ __global__ void __launch_bounds__(256) gradient_kernel(Params P) {
     const double xi = P.S.x[s], yi = P.S.y[s], zi = P.S.z[s], pmin = P.S.minp[s];
     int cnt = P.nbr_count[s];
     double gx = 0.0, gy = 0.0, gz = 0.0;
-    for (int k = 0; k < cnt; k++) {
-        double d = P.nbr_dist[SELL(k, s)];
-        if (d < re) {
-            int j = P.nbr_idx[SELL(k, s)];
-            if (P.S.type[j] == MPSB_DUMMY_WALL) continue;
-            double dp = P.S.p[j] - pmin, wgt = (re / d) - 1.0, d2 = d * d;
-            gx += (P.S.x[j] - xi) * dp * wgt / d2;
-            gy += (P.S.y[j] - yi) * dp * wgt / d2;
-            gz += (P.S.z[j] - zi) * dp * wgt / d2;
-        }
-    }
+    struct Nb { double x, y, z, p; int type; };
+    mpsb_walk_list<8, Nb>(
+        P, s, cnt, [&](int j) { return Nb{P.S.x[j], P.S.y[j], P.S.z[j], P.S.p[j], P.S.type[j]}; },
+        [&](int, double d, int, const Nb& q) {
+            if (d < re) {
+                if (q.type == MPSB_DUMMY_WALL) return;
+                double dp = q.p - pmin, wgt = (re / d) - 1.0, d2 = d * d;
+                gx += (q.x - xi) * dp * wgt / d2;
+                gy += (q.y - yi) * dp * wgt / d2;
+                gz += (q.z - zi) * dp * wgt / d2;
+            }
+        });
     gx *= P.grad_coef; gy *= P.grad_coef; gz *= P.grad_coef;
     P.S.ax[s] = -1.0 * gx / P.s.density;
     P.S.ay[s] = -1.0 * gy / P.s.density;

@@ -29,33 +29,55 @@ __global__ void __launch_bounds__(128) neighbor_kernel(Params P) {
     // A domain of zero thickness in z (every 2-D case) keeps all non-ghost particles at z == zmin, i.e. in the
     // plane iz == 1 (anything else is out of the domain and a ghost): the planes iz +- 1 are empty, skip them.
     const int zspan = P.s.domain_max[2] == P.s.domain_min[2] ? 0 : 1;
-    // not unrolled: 27 copies of the inner loop (with its inlined fp64 square root) overflow the instruction cache
+    // The cells are walked in the reference's order as one rolled loop q = (jx, jy, jz) (27 unrolled copies of
+    // the body would overflow the instruction cache). Two things keep a thread from waiting one memory round
+    // trip per candidate: the range of cell q + 1 is loaded before cell q is processed, and the candidates of
+    // a cell are loaded eight at a time (surplus slots clamped to the last particle of the cell and ignored).
+    const int nz_cells = 2 * zspan + 1, ncell = 9 * nz_cells;
+    auto cell_range = [&](int q, int& b, int& e) {
+        const int dx = q / (3 * nz_cells), r = q - dx * (3 * nz_cells), dy = r / nz_cells, dz = r - dy * nz_cells;
+        const int jx = ix - 1 + dx, jy = iy - 1 + dy, jz = iz - zspan + dz;
+        b = 0;
+        e = 0;
+        if (jx >= 0 && jx < P.numX && jy >= 0 && jy < P.numY && jz >= 0 && jz < P.numZ) {
+            const int c = jx + jy * P.numX + jz * nxy;
+            b = P.cell_start[c];
+            e = P.cell_end[c];
+        }
+    };
+    int nb, ne;
+    cell_range(0, nb, ne);
 #pragma unroll 1
-    for (int jx = ix - 1; jx <= ix + 1; jx++) {
-        if (jx < 0 || jx >= P.numX) continue;
+    for (int q = 0; q < ncell; q++) {
+        const int b = nb, e = ne;
+        if (q + 1 < ncell) cell_range(q + 1, nb, ne);
 #pragma unroll 1
-        for (int jy = iy - 1; jy <= iy + 1; jy++) {
-            if (jy < 0 || jy >= P.numY) continue;
-#pragma unroll 1
-            for (int jz = iz - zspan; jz <= iz + zspan; jz++) {
-                if (jz < 0 || jz >= P.numZ) continue;
-                int c = jx + jy * P.numX + jz * nxy;
-                int b = P.cell_start[c], e = P.cell_end[c];
-                for (int j = b; j < e; j++) {
-                    double dx = P.S.x[j] - xi, dy = P.S.y[j] - yi, dz = P.S.z[j] - zi;
-                    double d2 = (dx * dx + dy * dy) + dz * dz;
-                    // 70 % of the candidates of a 3x3(x3) cell block are out of range: skip their square root.
-                    // d2 >= re2_out implies sqrt(d2) >= re exactly, hence RN(sqrt(d2)) >= re: the reference's
-                    // `dist < re` is false for them whatever the rounding, so the kept set is unchanged.
-                    if (d2 >= re2_out) continue;
-                    double dist = sqrt(d2); // Eigen (pj - pi).norm()
-                    if (j != s && dist < re) {
-                        if (count < P.K) {
-                            P.nbr_idx[SELL(count, s)]  = j;
-                            P.nbr_dist[SELL(count, s)] = dist;
-                        }
-                        count++;
+        for (int j0 = b; j0 < e; j0 += 8) {
+            double X[8], Y[8], Z[8];
+#pragma unroll
+            for (int t = 0; t < 8; t++) {
+                const int j = min(j0 + t, e - 1);
+                X[t] = P.S.x[j];
+                Y[t] = P.S.y[j];
+                Z[t] = P.S.z[j];
+            }
+#pragma unroll
+            for (int t = 0; t < 8; t++) {
+                const int j = j0 + t;
+                if (j >= e) break;
+                double dx = X[t] - xi, dy = Y[t] - yi, dz = Z[t] - zi;
+                double d2 = (dx * dx + dy * dy) + dz * dz;
+                // 70 % of the candidates of a 3x3(x3) cell block are out of range: skip their square root.
+                // d2 >= re2_out implies sqrt(d2) >= re exactly, hence RN(sqrt(d2)) >= re: the reference's
+                // `dist < re` is false for them whatever the rounding, so the kept set is unchanged.
+                if (d2 >= re2_out) continue;
+                double dist = sqrt(d2); // Eigen (pj - pi).norm()
+                if (j != s && dist < re) {
+                    if (count < P.K) {
+                        P.nbr_idx[SELL(count, s)]  = j;
+                        P.nbr_dist[SELL(count, s)] = dist;
                     }
+                    count++;
                 }
             }
         }
@@ -81,9 +103,13 @@ __global__ void number_density_kernel(Params P) {
         const double re = P.s.re_pressure;
         int cnt = P.nbr_count[s];
         double n = 0.0;
-        for (int k = 0; k < cnt; k++) {
-            double d = P.nbr_dist[SELL(k, s)];
-            if (d < re) n += mpsb_weight(d, re);
+        for (int k0 = 0; k0 < cnt; k0 += 8) { // eight distance loads in flight, sum in list order
+            double d[8];
+#pragma unroll
+            for (int b = 0; b < 8; b++) d[b] = P.nbr_dist[SELL(min(k0 + b, cnt - 1), s)];
+#pragma unroll
+            for (int b = 0; b < 8; b++)
+                if (k0 + b < cnt && d[b] < re) n += mpsb_weight(d[b], re);
         }
         ratio = n / P.s.n0_pressure;
     }

@@ -22,10 +22,16 @@ __global__ void __launch_bounds__(256) flags_kernel(Params P) {
             const double re_s = P.s.re_surface, re_p = P.s.re_pressure;
             int cnt = P.nbr_count[s];
             double ns = 0.0, np = 0.0;
-            for (int k = 0; k < cnt; k++) {
-                double d = P.nbr_dist[SELL(k, s)];
-                if (d < re_s) ns += (re_s / d) - 1.0;
-                if (d < re_p) np += (re_p / d) - 1.0;
+            for (int k0 = 0; k0 < cnt; k0 += 8) { // distances only: eight loads in flight, sums in list order
+                double d[8];
+#pragma unroll
+                for (int b = 0; b < 8; b++) d[b] = P.nbr_dist[SELL(min(k0 + b, cnt - 1), s)];
+#pragma unroll
+                for (int b = 0; b < 8; b++)
+                    if (k0 + b < cnt) {
+                        if (d[b] < re_s) ns += (re_s / d[b]) - 1.0;
+                        if (d[b] < re_p) np += (re_p / d[b]) - 1.0;
+                    }
             }
             if (ns < P.beta_n0) {
                 bc = MPSB_BC_SURFACE;
@@ -51,17 +57,18 @@ __global__ void __launch_bounds__(256) source_ho_kernel(Params P) {
     const double ui = P.S.u[s], vi = P.S.v[s], wi = P.S.w[s];
     double b = P.src_ho0 * (P.S.ratio[s] - 1.0);
     int cnt = P.nbr_count[s];
-    for (int k = 0; k < cnt; k++) {
-        int j = P.nbr_idx[SELL(k, s)];
-        if (P.S.bc[j] == MPSB_BC_IGNORED) continue;
-        double d = P.nbr_dist[SELL(k, s)];
-        if (d < re) {
-            double rx = P.S.x[j] - xi, ry = P.S.y[j] - yi, rz = P.S.z[j] - zi;
-            double ux = P.S.u[j] - ui, uy = P.S.v[j] - vi, uz = P.S.w[j] - wi;
-            double ru = (rx * ux + ry * uy) + rz * uz;
-            b -= P.src_ho1 * ru / (d * d * d);
-        }
-    }
+    struct Nb { double x, y, z, u, v, w; int bc; };
+    mpsb_walk_list<4, Nb>(
+        P, s, cnt, [&](int j) { return Nb{P.S.x[j], P.S.y[j], P.S.z[j], P.S.u[j], P.S.v[j], P.S.w[j], P.S.bc[j]}; },
+        [&](int, double d, int, const Nb& q) {
+            if (q.bc == MPSB_BC_IGNORED) return;
+            if (d < re) {
+                double rx = q.x - xi, ry = q.y - yi, rz = q.z - zi;
+                double ux = q.u - ui, uy = q.v - vi, uz = q.w - wi;
+                double ru = (rx * ux + ry * uy) + rz * uz;
+                b -= P.src_ho1 * ru / (d * d * d);
+            }
+        });
     P.rhs[s] = b;
 }
 
@@ -80,26 +87,25 @@ __global__ void __launch_bounds__(256) matrix_kernel(Params P, int force_wide) {
     if (s < *P.n_active && P.S.bc[s] == MPSB_BC_INNER) {
         const double re = P.s.re_pressure;
         int cnt = P.nbr_count[s];
-        for (int k = 0; k < cnt; k++) {
-            double d = P.nbr_dist[SELL(k, s)];
-            if (d < re) {
-                int j   = P.nbr_idx[SELL(k, s)];
-                int bcj = P.S.bc[j];
-                if (bcj == MPSB_BC_IGNORED) continue;
-                double a = P.mat_coef * ((re / d) - 1.0) / P.s.density;
-                diag += a;
-                if (bcj == MPSB_BC_INNER) {
-                    P.ell_col[SELL(m, s)] = j;
-                    P.ell_val[SELL(m, s)] = -a;
-                    const int off = j - (s & ~31); // 16-bit form: offset from the slice's first row
-                    P.ell_col16[SELL(m, s)] = (short) off;
-                    if (off < -32768 || off > 32767) wide = 1;
-                    cmin = min(cmin, j);
-                    cmax = max(cmax, j);
-                    m++;
+        mpsb_walk_list<8, int>(
+            P, s, cnt, [&](int j) { return P.S.bc[j]; },
+            [&](int, double d, int j, const int& bcj) {
+                if (d < re) {
+                    if (bcj == MPSB_BC_IGNORED) return;
+                    double a = P.mat_coef * ((re / d) - 1.0) / P.s.density;
+                    diag += a;
+                    if (bcj == MPSB_BC_INNER) {
+                        P.ell_col[SELL(m, s)] = j;
+                        P.ell_val[SELL(m, s)] = -a;
+                        const int off = j - (s & ~31); // 16-bit form: offset from the slice's first row
+                        P.ell_col16[SELL(m, s)] = (short) off;
+                        if (off < -32768 || off > 32767) wide = 1;
+                        cmin = min(cmin, j);
+                        cmax = max(cmax, j);
+                        m++;
+                    }
                 }
-            }
-        }
+            });
         if (P.s.quasi_compressibility_on) diag += P.qc_term;
         atomicAdd(&P.stats->nnz, m + 1);
     }
@@ -154,18 +160,19 @@ __global__ void __launch_bounds__(256) dirichlet_union_kernel(Params P) {
     if (s >= *P.n_active) return;
     const double re = P.s.re_pressure;
     int cnt = P.nbr_count[s];
-    for (int k = 0; k < cnt; k++) {
-        int j = P.nbr_idx[SELL(k, s)];
-        if (j > s || !(P.nbr_dist[SELL(k, s)] < re)) continue; // each undirected edge once
-        int a = uf_find(P.parent, s), b = uf_find(P.parent, j);
-        while (a != b) {
-            if (a < b) { int t = a; a = b; b = t; }
-            int old = atomicCAS(&P.parent[a], a, b);
-            if (old == a) break;
-            a = uf_find(P.parent, old);
-            b = uf_find(P.parent, b);
-        }
-    }
+    mpsb_walk_list<8, MpsbNoRec>(
+        P, s, cnt, [](int) { return MpsbNoRec{}; },
+        [&](int, double d, int j, const MpsbNoRec&) {
+            if (j > s || !(d < re)) return; // each undirected edge once
+            int a = uf_find(P.parent, s), b = uf_find(P.parent, j);
+            while (a != b) {
+                if (a < b) { int t = a; a = b; b = t; }
+                int old = atomicCAS(&P.parent[a], a, b);
+                if (old == a) break;
+                a = uf_find(P.parent, old);
+                b = uf_find(P.parent, b);
+            }
+        });
 }
 
 __global__ void dirichlet_mark_kernel(Params P) {
@@ -197,15 +204,15 @@ __global__ void __launch_bounds__(256) min_pressure_kernel(Params P) {
     const double re = P.s.re_pressure;
     double m = P.S.p[s];
     int cnt  = P.nbr_count[s];
-    for (int k = 0; k < cnt; k++) {
-        double d = P.nbr_dist[SELL(k, s)];
-        if (d < re) {
-            int j = P.nbr_idx[SELL(k, s)];
-            if (P.S.type[j] == MPSB_DUMMY_WALL) continue;
-            double pj = P.S.p[j];
-            if (m > pj) m = pj;
-        }
-    }
+    struct Nb { double p; int type; };
+    mpsb_walk_list<8, Nb>(
+        P, s, cnt, [&](int j) { return Nb{P.S.p[j], P.S.type[j]}; },
+        [&](int, double d, int, const Nb& q) {
+            if (d < re) {
+                if (q.type == MPSB_DUMMY_WALL) return;
+                if (m > q.p) m = q.p;
+            }
+        });
     P.S.minp[s] = m;
 }
 

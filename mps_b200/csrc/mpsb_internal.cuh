@@ -213,4 +213,31 @@ __host__ __device__ __forceinline__ size_t mpsb_sell(int k, int s, int K) {
 __device__ __forceinline__ double mpsb_weight(double dist, double re) {
     return dist < re ? (re / dist) - 1.0 : 0.0;
 }
+
+// Walk the neighbour list of SORTED row s in list order, NB entries at a time: the (distance, index) loads
+// of a batch are issued together, then everything `fetch(j)` gathers for them, and only then `use(k, d, j,
+// rec)` runs for k ascending — so sums keep the reference's order, but a thread waits for two memory round
+// trips per batch instead of three per neighbour (load d -> branch -> load j -> gather). The per-particle
+// kernels are latency chains, not bandwidth: this is what sets their time at every size. Loads of the
+// surplus slots of the last batch are clamped to the last entry (always inside the list) and ignored.
+template <int NB, class Rec, class Fetch, class Use>
+__device__ __forceinline__ void mpsb_walk_list(const Params& P, int s, int cnt, Fetch fetch, Use use) {
+    for (int k0 = 0; k0 < cnt; k0 += NB) {
+        double d[NB];
+        int j[NB];
+        Rec r[NB];
+#pragma unroll
+        for (int b = 0; b < NB; b++) {
+            const int k = min(k0 + b, cnt - 1);
+            d[b] = P.nbr_dist[SELL(k, s)];
+            j[b] = P.nbr_idx[SELL(k, s)];
+        }
+#pragma unroll
+        for (int b = 0; b < NB; b++) r[b] = fetch(j[b]);
+#pragma unroll
+        for (int b = 0; b < NB; b++)
+            if (k0 + b < cnt) use(k0 + b, d[b], j[b], r[b]);
+    }
+}
+struct MpsbNoRec {};
 #endif
