@@ -11,6 +11,8 @@
  *   MPSB_MAX_NEIGHBORS=<K>       neighbour-list / PPE row capacity (default 64 in 2-D, 384 in 3-D)
  *   MPSB_NO_CLUSTER_SOLVE=1      never use the small-system cluster solve (csrc/k_pcg_cluster.cu)
  *   MPSB_NO_STEP_GRAPH=1         issue the step's launches directly instead of replaying a CUDA graph
+ *   MPSB_SMALL_BUILD_MAX_N=<n>   build cell lists in one single-CTA launch up to n particles (default 2048, at most
+ *                                32 768; 0 = always the multi-launch radix sort)
  *   MPSB_FORCE_WIDE_COLUMNS=1    stream int32 PPE columns even when 16-bit offsets fit
  *   MPSB_CG_ITERATION_CAP=<n>    stop the solve after n iterations (profiling a bounded solve)
  * and by the host mirror (mps_b200/host): MPSB_DEVICE=<ordinal>, MPSB_CSV_FLOAT=gcc5.

@@ -20,14 +20,7 @@ constexpr int RADIX        = 256;
 // reference's 27-cell scan index outside its arrays raises the out-of-grid flag (SURVEY B-8).
 // It also clears the cell ranges and the active count of the previous build (they are rewritten by
 // cell_range_kernel, several kernels later), which saves three memset nodes per build.
-__global__ void key_kernel(Params P) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    for (int c = i; c < P.numCells; c += gridDim.x * blockDim.x) {
-        P.cell_start[c] = 0;
-        P.cell_end[c]   = 0;
-    }
-    if (i == 0) *P.n_active = 0;
-    if (i >= P.N) return;
+__device__ __forceinline__ unsigned cell_key_of(const Params& P, int i) {
     unsigned key = MPSB_GHOST_KEY;
     if (P.H.type[i] != MPSB_GHOST) {
         double len = P.s.re_max;
@@ -43,7 +36,18 @@ __global__ void key_kernel(Params P) {
         }
         key = (unsigned) (ix + iy * P.numX + iz * P.numX * P.numY);
     }
-    P.key[i] = key;
+    return key;
+}
+
+__global__ void key_kernel(Params P) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    for (int c = i; c < P.numCells; c += gridDim.x * blockDim.x) {
+        P.cell_start[c] = 0;
+        P.cell_end[c]   = 0;
+    }
+    if (i == 0) *P.n_active = 0;
+    if (i >= P.N) return;
+    P.key[i] = cell_key_of(P, i);
     P.val[i] = i;
 }
 
@@ -202,9 +206,7 @@ __global__ void cell_range_kernel(Params P) {
 }
 
 // HOME (id order) -> SORTED (cell order) for every field; also perm and its inverse.
-__global__ void gather_all_kernel(Params P, int from_val) {
-    int s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= P.N) return;
+__device__ __forceinline__ void gather_row(const Params& P, int s, int from_val) {
     int id = from_val ? P.val[s] : P.S.id[s];
     if (from_val) {
         P.S.id[s]   = id;
@@ -217,11 +219,13 @@ __global__ void gather_all_kernel(Params P, int from_val) {
     P.S.p[s] = H.p[id]; P.S.minp[s] = H.minp[id]; P.S.ratio[s] = H.ratio[id];
     P.S.type[s] = H.type[id]; P.S.bc[s] = H.bc[id];
 }
+__global__ void gather_all_kernel(Params P, int from_val) {
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s < P.N) gather_row(P, s, from_val);
+}
 
 // SORTED -> HOME.
-__global__ void scatter_all_kernel(Params P) {
-    int s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= P.N) return;
+__device__ __forceinline__ void scatter_row(const Params& P, int s) {
     int id = P.S.id[s];
     const Home& H = P.H;
     H.pos[3 * id] = P.S.x[s]; H.pos[3 * id + 1] = P.S.y[s]; H.pos[3 * id + 2] = P.S.z[s];
@@ -229,6 +233,113 @@ __global__ void scatter_all_kernel(Params P) {
     H.acc[3 * id] = P.S.ax[s]; H.acc[3 * id + 1] = P.S.ay[s]; H.acc[3 * id + 2] = P.S.az[s];
     H.p[id] = P.S.p[s]; H.minp[id] = P.S.minp[s]; H.ratio[id] = P.S.ratio[s];
     H.type[id] = P.S.type[s]; H.bc[id] = P.S.bc[s];
+}
+__global__ void scatter_all_kernel(Params P) {
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s < P.N) scatter_row(P, s);
+}
+
+// ---- small systems: the whole build in ONE launch ----------------------------------------------------
+// The shipped cases (458 - 6 146 particles) are bound by the length of the launch chain, and the build above
+// is 10 launches, three times per step. Up to small_build_max_n particles one CTA does all of it, phases
+// separated by __syncthreads: (0) SORTED -> HOME when the sorted copy is newer, (1) keys and per-cell
+// counts, (2) exclusive scan of the counts, (3) placement with per-cell cursors (any order), (4) ids put in
+// ascending order inside every cell (rank = smaller ids of the same cell) and the ghost tail (a scan), (5) sorted keys,
+// perm, inverse perm and HOME -> SORTED. A stable sort by key has exactly one result, so every array the
+// rest of the step reads is identical to the radix path's (empty cells: start == end instead of 0, 0).
+constexpr int SMALL_BUILD_THREADS = 1024;
+constexpr int SMALL_BUILD_MAX_CELLS = 1 << 18; // the particle limit is h->small_build_max_n
+
+__device__ __forceinline__ int block_exclusive_scan(int v, int* warp_sums, int& total) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        int t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    __syncthreads(); // warp_sums may still be read from an earlier call
+    if (lane == 31) warp_sums[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        int ws = warp_sums[lane], wi = ws;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int t = __shfl_up_sync(0xffffffffu, wi, o);
+            if (lane >= o) wi += t;
+        }
+        warp_sums[lane] = wi - ws;
+        if (lane == 31) warp_sums[32] = wi;
+    }
+    __syncthreads();
+    total = warp_sums[32];
+    return warp_sums[warp] + incl - v;
+}
+
+__global__ void __launch_bounds__(SMALL_BUILD_THREADS) small_cell_build_kernel(Params P, int scatter_first) {
+    __shared__ int warp_sums[33];
+    const int T = SMALL_BUILD_THREADS, tid = threadIdx.x, N = P.N, C = P.numCells;
+    unsigned* key_by_id = P.key_alt; // scratch: key of particle id
+    int* cursor         = P.cell_end;
+    // (0) + clear the counts
+    if (scatter_first)
+        for (int s = tid; s < N; s += T) scatter_row(P, s);
+    for (int c = tid; c < C; c += T) cursor[c] = 0;
+    __syncthreads();
+    // (1) keys, counts
+    for (int i = tid; i < N; i += T) {
+        unsigned k   = cell_key_of(P, i);
+        key_by_id[i] = k;
+        if (k != MPSB_GHOST_KEY) atomicAdd(&cursor[k], 1);
+    }
+    __syncthreads();
+    // (2) scan: a contiguous chunk of cells per thread
+    const int per = (C + T - 1) / T, c0 = min(tid * per, C), c1 = min(c0 + per, C);
+    int sum = 0;
+    for (int c = c0; c < c1; c++) sum += cursor[c];
+    int n_active;
+    int off = block_exclusive_scan(sum, warp_sums, n_active);
+    for (int c = c0; c < c1; c++) {
+        int cnt         = cursor[c];
+        P.cell_start[c] = off;
+        cursor[c]       = off; // advanced back to start + count by the placement
+        off += cnt;
+    }
+    // ghosts keep id order at the tail: rank = number of ghosts with a smaller id (chunked scan over ids)
+    const int iper = (N + T - 1) / T, i0 = min(tid * iper, N), i1 = min(i0 + iper, N);
+    int g = 0;
+    for (int i = i0; i < i1; i++) g += key_by_id[i] == MPSB_GHOST_KEY;
+    int n_ghost;
+    int goff = n_active + block_exclusive_scan(g, warp_sums, n_ghost);
+    for (int i = i0; i < i1; i++)
+        if (key_by_id[i] == MPSB_GHOST_KEY) P.val_alt[goff++] = i;
+    __syncthreads();
+    // (3) placement
+    for (int i = tid; i < N; i += T) {
+        unsigned k = key_by_id[i];
+        if (k != MPSB_GHOST_KEY) P.val_alt[atomicAdd(&cursor[k], 1)] = i;
+    }
+    __syncthreads();
+    // (4) ids ascending inside every cell: the final place of an id is the cell's start plus the number of
+    // smaller ids in the cell (independent loads, no sorting loop); ghosts are in order already
+    for (int s = tid; s < N; s += T) {
+        const int v      = P.val_alt[s];
+        const unsigned k = key_by_id[v];
+        int dst          = s;
+        if (k != MPSB_GHOST_KEY) {
+            const int b = P.cell_start[k], e = cursor[k];
+            dst = b;
+            for (int q = b; q < e; q++) dst += P.val_alt[q] < v;
+        }
+        P.val[dst] = v;
+    }
+    if (tid == 0) *P.n_active = n_active;
+    __syncthreads();
+    // (5) sorted keys, perm, state
+    for (int s = tid; s < N; s += T) {
+        P.key[s] = key_by_id[P.val[s]];
+        gather_row(P, s, 1);
+    }
 }
 
 } // namespace
@@ -243,10 +354,15 @@ void mpsb_launch_scatter_all(mpsb_handle* h) {
     MPSB_LAUNCH(h, scatter_all_kernel, mpsb_div_up(P.N, 256), 256, 0, P);
 }
 
-// HOME must be current (the caller scatters first when the sorted copy is newer).
-void mpsb_launch_cell_build(mpsb_handle* h) {
+// scatter_first: the SORTED copy is newer than HOME (it was modified since the last scatter).
+void mpsb_launch_cell_build(mpsb_handle* h, bool scatter_first) {
     Params& P   = h->P;
     int N       = P.N;
+    if (N <= h->small_build_max_n && P.numCells <= 8 * h->small_build_max_n && P.numCells <= SMALL_BUILD_MAX_CELLS) {
+        MPSB_LAUNCH(h, small_cell_build_kernel, 1, SMALL_BUILD_THREADS, 0, P, scatter_first ? 1 : 0);
+        return;
+    }
+    if (scatter_first) mpsb_launch_scatter_all(h);
     int grid    = mpsb_div_up(N, 256);
     int tiles   = mpsb_div_up(N, SORT_TILE);
     MPSB_LAUNCH(h, key_kernel, grid, 256, 0, P);

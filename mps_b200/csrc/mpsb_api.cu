@@ -96,8 +96,8 @@ void fill_stats(mpsb_handle* h, mpsb_step_stats* st) {
     st->courant_exceeds_cfl = d.courant_bits_as_double > h->P.s.cfl_condition;
 }
 
-void build_lists(mpsb_handle* h) {
-    mpsb_launch_cell_build(h);
+void build_lists(mpsb_handle* h, bool scatter_first = false) {
+    mpsb_launch_cell_build(h, scatter_first);
     mpsb_launch_neighbors(h);
     h->have_lists = true;
 }
@@ -214,6 +214,9 @@ int mpsb_create(const mpsb_settings* settings, int64_t n, const int32_t* type, c
         const char* ng = getenv("MPSB_NO_STEP_GRAPH");
         h->graph_enable = ng && atoi(ng) ? 0 : 1;
         h->n_graphs     = 0;
+        const char* nb = getenv("MPSB_SMALL_BUILD_MAX_N");
+        h->small_build_max_n = nb ? atoi(nb) : 2048;
+        if (h->small_build_max_n > 32768) h->small_build_max_n = 32768;
     }
     // initial state: type/position/velocity from the caller, everything else 0 / Ignored (SURVEY B-1)
     CKC(cudaMemcpy(H.type, type, sizeof(int) * (size_t) n, cudaMemcpyHostToDevice));
@@ -328,13 +331,11 @@ static int issue_step(mpsb_handle* h, int want_number_density, bool timed) {
     EV(1);
     mpsb_launch_explicit(h);                         // calcGravity, calcViscosity, moveParticles
     EV(2);
-    mpsb_launch_scatter_all(h);
-    build_lists(h);                                  // setNeighbors
+    build_lists(h, true);                                  // setNeighbors
     EV(3);
     mpsb_launch_collision(h);                        // collision
     EV(4);
-    mpsb_launch_scatter_all(h);
-    build_lists(h);                                  // setNeighbors
+    build_lists(h, true);                                  // setNeighbors
     EV(5);
     mpsb_launch_flags_source(h);                     // calcPressure ...
     mpsb_launch_matrix(h);
@@ -350,8 +351,7 @@ static int issue_step(mpsb_handle* h, int want_number_density, bool timed) {
     mpsb_launch_gradient_move(h);                    // calcPressureGradient, moveParticlesWithPressureGradient
     EV(8);
     if (want_number_density) {                       // setNumberDensity (:125-127)
-        mpsb_launch_scatter_all(h);
-        build_lists(h);
+        build_lists(h, true);
         mpsb_launch_number_density(h);
     }
     EV(9);

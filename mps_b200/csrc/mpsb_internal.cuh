@@ -157,6 +157,7 @@ struct mpsb_handle {
     int cl_size, cl_smem;   // cluster solve for small systems (k_pcg_cluster.cu): cluster size (0 = unavailable), dynamic smem
     int cl_launched;        // the cluster kernel has run on this handle (*cluster_done may be set)
     int cl_disable;         // MPSB_NO_CLUSTER_SOLVE=1: always use the grid kernel (tests)
+    int small_build_max_n;  // single-launch cell build up to this many particles (MPSB_SMALL_BUILD_MAX_N; 0 = never)
     int in_step;            // inside mpsb_step: DevStats was cleared as a whole, launchers skip their own clears
     int graph_enable;       // small cases: replay the step as one CUDA graph (MPSB_NO_STEP_GRAPH=1 disables)
     int n_graphs;
@@ -173,7 +174,7 @@ struct mpsb_handle {
 };
 
 // ---- launchers (each file owns its kernels) ----------------------------------------------------
-void mpsb_launch_cell_build(mpsb_handle* h);            // k_cells.cu: scatter->key->sort->ranges->gather
+void mpsb_launch_cell_build(mpsb_handle* h, bool scatter_first); // k_cells.cu: [scatter->]key->sort->ranges->gather
 void mpsb_launch_gather_all(mpsb_handle* h);            // HOME -> SORTED with the current perm
 void mpsb_launch_scatter_all(mpsb_handle* h);           // SORTED -> HOME
 void mpsb_launch_neighbors(mpsb_handle* h);             // k_neighbors.cu

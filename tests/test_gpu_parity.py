@@ -347,6 +347,29 @@ def test_graph_replayed_step_is_bitwise_the_directly_issued_step(monkeypatch):
     assert out[0][4] > 0.0 and out[1][4] > 0.0  # the solve is timed on both paths
 
 
+@pytest.mark.parametrize("case", ["dambreak", "hydrostatic", "tank3d"])
+def test_single_launch_cell_build_is_bitwise_the_radix_build(case, monkeypatch):
+    """Small systems build the cell list in one single-CTA launch (counting sort by cell + ids put in order
+    inside each cell) instead of the multi-launch radix sort: a stable sort has one result, so free
+    runs are identical bit for bit — including steps where particles turn into ghosts (dambreak) — and so
+    are the neighbour lists."""
+    S, t, p, v = C.load_case(case)
+    out = []
+    for max_n in ("32768", "0"):
+        monkeypatch.setenv("MPSB_SMALL_BUILD_MAX_N", max_n)
+        dev = capi.DeviceMPS(S, t, p, v)
+        dev.load_initial_state()
+        cour = [dev.step_forward(k % 9 == 0) for k in range(30)]
+        out.append((dev.download(), cour, dev.neighbors(), dev.launch_count))
+        dev.close()
+    for name in U.STATE_FIELDS:
+        assert np.array_equal(out[0][0][name], out[1][0][name]), name
+    assert out[0][1] == out[1][1]
+    for a, b in zip(out[0][2], out[1][2]):
+        assert np.array_equal(a, b)
+    assert out[0][3] < out[1][3]  # fewer launches
+
+
 def test_full_size_case_properties():
     """BASELINE configs[3] at its full size (nx = 2832, 4.04 M particles): the oracle would take the best part
     of an hour per step there, so the path is checked through size-independent properties of the domain —
