@@ -36,3 +36,14 @@ def test_gpu_arm_refuses_to_run_without_a_gpu():
     r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--steps", "1", "--warmup", "0", "--nx", "80"],
                        capture_output=True, text=True, timeout=600, cwd=ROOT)
     assert r.returncode != 0 and "no CPU path" in r.stderr + r.stdout
+
+
+def test_library_chatter_on_stdout_does_not_reach_the_json_line():
+    """NCCL prints a version banner on the C-level stdout of every rank; bench.py points fd 1 at stderr and writes
+    its one JSON line to a private duplicate of the original stdout."""
+    code = ("import os, sys; sys.path.insert(0, %r); import bench; bench._claim_stdout(); "
+            "os.write(1, b'NCCL version x.y\\n'); print('python-level chatter'); bench._emit({'metric': 'm', 'value': 1})") % ROOT
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=120, cwd=ROOT)
+    assert r.returncode == 0, r.stderr
+    assert r.stdout == '{"metric": "m", "value": 1}\n'
+    assert "NCCL version x.y" in r.stderr and "python-level chatter" in r.stderr
