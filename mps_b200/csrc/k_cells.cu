@@ -39,7 +39,11 @@ __device__ __forceinline__ unsigned cell_key_of(const Params& P, int i) {
     return key;
 }
 
-__global__ void key_kernel(Params P) {
+__device__ __forceinline__ void scatter_row(const Params& P, int s);
+
+// scatter_first: thread i first writes SORTED row i back to HOME (the sorted copy is newer) and then keys the
+// particle that row belongs to — one launch instead of scatter_all_kernel + key_kernel.
+__global__ void key_kernel(Params P, int scatter_first) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     for (int c = i; c < P.numCells; c += gridDim.x * blockDim.x) {
         P.cell_start[c] = 0;
@@ -47,8 +51,13 @@ __global__ void key_kernel(Params P) {
     }
     if (i == 0) *P.n_active = 0;
     if (i >= P.N) return;
-    P.key[i] = cell_key_of(P, i);
-    P.val[i] = i;
+    int id = i;
+    if (scatter_first) {
+        scatter_row(P, i);
+        id = P.S.id[i];
+    }
+    P.key[id] = cell_key_of(P, id);
+    P.val[id] = id;
 }
 
 // Ghost keys map to digit 255 in every pass so they stay at the tail for any number of passes.
@@ -193,16 +202,21 @@ __global__ void radix_scatter_kernel(const unsigned* __restrict__ key_in, const 
     }
 }
 
-// cell_start / cell_end from the sorted keys, and the number of non-ghost particles.
-__global__ void cell_range_kernel(Params P) {
+__device__ __forceinline__ void gather_row(const Params& P, int s, int from_val);
+
+// cell_start / cell_end from the sorted keys, the number of non-ghost particles, and (same thread, same row)
+// perm, inverse perm and HOME -> SORTED for every field.
+__global__ void cell_range_gather_kernel(Params P) {
     int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= P.N) return;
     unsigned k = P.key[s];
-    if (k == MPSB_GHOST_KEY) return;
-    if (s == 0 || P.key[s - 1] != k) P.cell_start[k] = s;
-    unsigned next = (s == P.N - 1) ? MPSB_GHOST_KEY : P.key[s + 1];
-    if (next != k) P.cell_end[k] = s + 1;
-    if (next == MPSB_GHOST_KEY) *P.n_active = s + 1;
+    if (k != MPSB_GHOST_KEY) {
+        if (s == 0 || P.key[s - 1] != k) P.cell_start[k] = s;
+        unsigned next = (s == P.N - 1) ? MPSB_GHOST_KEY : P.key[s + 1];
+        if (next != k) P.cell_end[k] = s + 1;
+        if (next == MPSB_GHOST_KEY) *P.n_active = s + 1;
+    }
+    gather_row(P, s, 1);
 }
 
 // HOME (id order) -> SORTED (cell order) for every field; also perm and its inverse.
@@ -362,10 +376,9 @@ void mpsb_launch_cell_build(mpsb_handle* h, bool scatter_first) {
         MPSB_LAUNCH(h, small_cell_build_kernel, 1, SMALL_BUILD_THREADS, 0, P, scatter_first ? 1 : 0);
         return;
     }
-    if (scatter_first) mpsb_launch_scatter_all(h);
     int grid    = mpsb_div_up(N, 256);
     int tiles   = mpsb_div_up(N, SORT_TILE);
-    MPSB_LAUNCH(h, key_kernel, grid, 256, 0, P);
+    MPSB_LAUNCH(h, key_kernel, grid, 256, 0, P, scatter_first ? 1 : 0);
     for (int shift = 0; shift < h->sort_bits; shift += 8) {
         MPSB_LAUNCH(h, radix_hist_kernel, tiles, SORT_THREADS, 0, P.key, N, shift, tiles, h->block_hist);
         MPSB_LAUNCH(h, exclusive_scan_kernel, 1, 1024, 0, h->block_hist, RADIX * tiles);
@@ -374,6 +387,5 @@ void mpsb_launch_cell_build(mpsb_handle* h, bool scatter_first) {
         unsigned* tk = P.key; P.key = P.key_alt; P.key_alt = tk;
         int* tv = P.val; P.val = P.val_alt; P.val_alt = tv;
     }
-    MPSB_LAUNCH(h, cell_range_kernel, grid, 256, 0, P);
-    MPSB_LAUNCH(h, gather_all_kernel, grid, 256, 0, P, 1);
+    MPSB_LAUNCH(h, cell_range_gather_kernel, grid, 256, 0, P);
 }
