@@ -4,9 +4,12 @@
 //   host_selftest float <style> <value>...           spelling of doubles (style: fixed6 | gcc5)
 //   host_selftest rendezvous x                       RANK/WORLD_SIZE/MASTER_* from the environment: share a 128-byte id, print its sum
 //   host_selftest exportbench <n> <out dir>          time Exporter::toCsv / toVtu on n synthetic particles (SURVEY f-1)
+//   host_selftest state <n> <file>                   binary state: write n particles, read back, compare bit for bit;
+//                                                    a truncated copy and a wrong magic must be refused
 #include "exporter.hpp"
 #include "mps.hpp"
 #include "rendezvous.hpp"
+#include "state_io.hpp"
 
 #include <chrono>
 #include <cstdint>
@@ -41,6 +44,52 @@ int main(int argc, char** argv) {
         for (int i = 0; i < 128; i++) sum += id[i] * (unsigned) (i + 1);
         std::printf("rank %d of %d sum %u\n", env.rank, env.world, sum);
         return 0;
+    }
+    if (mode == "state" && argc >= 4) {
+        const long n = std::atol(argv[2]);
+        const std::filesystem::path path(argv[3]);
+        std::vector<Particle> ps;
+        for (long i = 0; i < n; i++) {
+            // awkward values on purpose: denormals, negative zero, values no decimal CSV would carry
+            const double x = 1e-4 * (double) i / 3.0, y = -0.0, z = 4.9e-324 * (double) (i % 3);
+            ps.push_back(Particle((int) i, static_cast<ParticleType>((int) (i % 4) - 1), Eigen::Vector3d(x, y, z),
+                                  Eigen::Vector3d(-x, 1.0 / (double) (i + 1), 0.1 + (double) i), 1000.0));
+            ps.back().pressure           = 1e300 / (double) (i + 1);
+            ps.back().numberDensityRatio = 1.0 - 1e-16 * (double) i;
+            ps.back().boundaryCondition  = static_cast<BoundaryCondition>((int) (i % 3));
+        }
+        const double time = 0.1 + 0.2; // 0.30000000000000004
+        if (!state_io::write(path, time, ps)) return 1;
+        std::vector<Particle> back;
+        double t2 = 0.0;
+        if (!state_io::read(path, t2, back, 1000.0) || back.size() != ps.size() || std::memcmp(&t2, &time, 8) != 0) return 1;
+        long bad = 0;
+        for (std::size_t i = 0; i < ps.size(); i++) {
+            const Particle &a = ps[i], &b = back[i];
+            bool same = a.id == b.id && a.type == b.type && a.boundaryCondition == b.boundaryCondition &&
+                        std::memcmp(&a.pressure, &b.pressure, 8) == 0 &&
+                        std::memcmp(&a.numberDensityRatio, &b.numberDensityRatio, 8) == 0;
+            for (int k = 0; k < 3; k++) {
+                const double pa = a.position[k], pb = b.position[k], va = a.velocity[k], vb = b.velocity[k];
+                same = same && std::memcmp(&pa, &pb, 8) == 0 && std::memcmp(&va, &vb, 8) == 0;
+            }
+            bad += !same;
+        }
+        // refusals: a file cut short, and a file that is not a state file
+        const auto bytes = std::filesystem::file_size(path);
+        std::filesystem::path cut = path;
+        cut += ".cut";
+        std::filesystem::copy_file(path, cut, std::filesystem::copy_options::overwrite_existing);
+        if (n > 0) std::filesystem::resize_file(cut, bytes - 5);
+        const bool cut_refused = n == 0 || !state_io::read(cut, t2, back, 1000.0);
+        std::FILE* f = std::fopen(cut.string().c_str(), "wb");
+        std::fputs("id,type,x,y,z\n0,0,0,0,0\n", f);
+        std::fclose(f);
+        const bool text_refused = !state_io::read(cut, t2, back, 1000.0);
+        std::filesystem::remove(cut);
+        std::printf("particles %ld bytes %llu mismatches %ld truncated_refused %d text_refused %d\n", n,
+                    (unsigned long long) bytes, bad, (int) cut_refused, (int) text_refused);
+        return bad == 0 && cut_refused && text_refused ? 0 : 1;
     }
     if (mode == "exportbench" && argc >= 4) {
         const long n = std::atol(argv[2]);

@@ -227,6 +227,16 @@ def test_checkpoint_restart_is_bitwise_an_uninterrupted_run(tmp_path):
         assert np.array_equal(second[k], straight[k]), k
 
 
+@pytest.mark.parametrize("n", [0, 1, 1000])
+def test_binary_state_round_trips_bitwise_and_refuses_damaged_files(n, tmp_path):
+    """host/state_io.hpp on the CPU: denormals, -0.0, 0.1 + 0.2 and 1e300 come back bit for bit; a truncated file
+    and a CSV under the same name are refused."""
+    r = _run(SELFTEST, "state", str(n), str(tmp_path / "state.bin"))
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert r.stdout.split() == ["particles", str(n), "bytes", str(24 + 72 * n), "mismatches", "0",
+                                "truncated_refused", "1", "text_refused", "1"]
+
+
 def test_cpp_rendezvous_shares_the_id_between_three_processes():
     """host/rendezvous.hpp: rank 0 serves a 128-byte id over TCP on MASTER_PORT + 1, the others fetch it."""
     port = 30100 + os.getpid() % 500
