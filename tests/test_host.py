@@ -87,6 +87,21 @@ def test_float_spellings():
     assert r.stdout.split() == ["0.300000", "-1.250000", "2.000000", "0.000000"]
 
 
+def test_fixed6_spelling_equals_printf_for_random_doubles():
+    """The exporter formats with std::to_chars (fast path); the reference's clang build goes through
+    std::to_string = printf("%f"). Same bytes for 4 000 doubles over 30 decades, both signs, ties included."""
+    import numpy as np
+
+    rng = np.random.default_rng(11)
+    vals = np.concatenate([rng.standard_normal(2000) * 10.0 ** rng.integers(-12, 18, 2000),
+                           np.round(rng.standard_normal(1000), 6) + 5e-7,  # neighbours of rounding ties
+                           rng.integers(-10**6, 10**6, 1000) / 64.0])      # exactly representable fractions
+    args = [repr(float(x)) for x in vals]
+    r = _run(SELFTEST, "float", "fixed6", *args)
+    assert r.returncode == 0
+    assert r.stdout.split() == ["%f" % float(a) for a in args]
+
+
 def test_yaml_errors_are_fatal_and_named(tmp_path):
     bad = tmp_path / "settings.yml"
     bad.write_text("dim: 2\nparticle distance: 0.01\n")
