@@ -102,6 +102,28 @@ def test_fixed6_spelling_equals_printf_for_random_doubles():
     assert r.stdout.split() == ["%f" % float(a) for a in args]
 
 
+def test_gcc5_spelling_equals_the_reference_csv_writer_for_random_doubles():
+    """MPSB_CSV_FLOAT=gcc5 must spell doubles as a gcc build of the reference does: csv-parser's own digit-by-digit
+    routine (csv.hpp:6636-6681), here run from the reference's header itself (oracle/_ref/csv_float.exe)."""
+    import numpy as np
+
+    probe = os.path.join(ROOT, "oracle", "_ref", "csv_float.exe")
+    if not os.path.exists(probe):
+        pytest.skip("oracle/_ref/csv_float.exe not built (reference sources absent)")
+    rng = np.random.default_rng(12)
+    vals = np.concatenate([rng.standard_normal(2000) * 10.0 ** rng.integers(-8, 16, 2000),
+                           np.round(rng.standard_normal(1000), 5),              # values on the 5-decimal grid
+                           rng.integers(-10**7, 10**7, 500).astype(float),      # integers
+                           10.0 ** rng.integers(-6, 15, 200), [0.0, -0.0, 0.99999, 0.999999, 9.999995, 1e15, 123456789012345678.0]])
+    args = [repr(float(x)) for x in vals]
+    ours = _run(SELFTEST, "float", "gcc5", *args)
+    ref = _run(probe, *args)
+    assert ours.returncode == 0 and ref.returncode == 0
+    a, b = ours.stdout.split(), ref.stdout.split()
+    bad = [(x, y, z) for x, y, z in zip(args, a, b) if y != z]
+    assert len(a) == len(b) == len(args) and not bad, bad[:10]
+
+
 def test_yaml_errors_are_fatal_and_named(tmp_path):
     bad = tmp_path / "settings.yml"
     bad.write_text("dim: 2\nparticle distance: 0.01\n")
