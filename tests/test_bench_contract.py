@@ -47,3 +47,16 @@ def test_library_chatter_on_stdout_does_not_reach_the_json_line():
     assert r.returncode == 0, r.stderr
     assert r.stdout == '{"metric": "m", "value": 1}\n'
     assert "NCCL version x.y" in r.stderr and "python-level chatter" in r.stderr
+
+
+def test_reference_arm_under_torchrun_prints_one_line_from_rank_0():
+    """Launched the way the driver launches N > 1: rank 0 alone runs the CPU arm and prints, rank 1 exits 0."""
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29735", os.path.join(ROOT, "bench.py"),
+                        "--impl", "reference", "--gpus", "2", "--steps", "1", "--warmup", "0", "--nx", "80", "--cpu-nx", "80"],
+                       capture_output=True, text=True, timeout=900, cwd=ROOT)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [ln for ln in r.stdout.splitlines() if ln.strip()]
+    assert len(lines) == 1, r.stdout
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["n_gpus"] == 2 and d["value"] > 0
