@@ -37,12 +37,20 @@ DEFAULT_NX = 2832
 CPU_SAMPLE_NX = 400  # 84 518 particles: ~10 s per reference step on one Xeon core
 
 
-def workload_config(nx, n_particles, parallelism):
+def workload_config(nx, n_particles, parallelism, nx_timed=None, n_timed=None):
+    """`nx_fluid` / `particles` name BASELINE configs[3]; `nx_fluid_timed` / `particles_timed` are what THIS line
+    actually ran (they differ only on the CPU arm, which times a reduced-size sample of the same generator)."""
+    nx_timed = nx if nx_timed is None else nx_timed
+    n_timed = n_particles if n_timed is None else n_timed
     return {
         "workload": f"synthetic scaled dam break (BASELINE configs[3]): dambreak_fine geometry/settings, "
                     f"l0=0.4/{nx}, dt/l0=0.125 s/m",
         "nx_fluid": nx,
         "particles": int(n_particles),
+        "nx_fluid_timed": int(nx_timed),
+        "particles_timed": int(n_timed),
+        "reduced_size_sample": bool(nx_timed != nx),
+        "extrapolated": False,
         "parallelism": parallelism,
         "l2_policy": "working set (neighbour lists + PPE, >4 GB at nx=2832) exceeds the 126 MB L2; no flush needed",
     }
@@ -127,8 +135,21 @@ def make_cpu_mps(nx):
     return R.OracleMPS(S.to_c(), t, p, v), "port", int(np.count_nonzero(t != C.GHOST))
 
 
-def time_cpu_steps(nx, steps, warmup, budget_s=None):
+def set_omp_threads(k):
+    """OpenMP thread count of the already-loaded libgomp (the one libmps_ref.so is linked against)."""
+    import ctypes
+
+    try:
+        ctypes.CDLL("libgomp.so.1").omp_set_num_threads(int(k))
+        return True
+    except OSError:
+        return False
+
+
+def time_cpu_steps(nx, steps, warmup, budget_s=None, threads=None):
     mps, kind, n_active = make_cpu_mps(nx)
+    if threads is not None:
+        set_omp_threads(threads)
     for _ in range(warmup):
         mps.step(False)
     times = []
@@ -143,11 +164,64 @@ def time_cpu_steps(nx, steps, warmup, budget_s=None):
     return kind, n_active, times
 
 
+def cpu_model_name():
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("model name"):
+                return line.split(":", 1)[1].strip()
+    except OSError:
+        pass
+    return "unknown"
+
+
 def cpu_sample_text(nx, n, kind, nsteps):
     what = ("the unmodified reference (oracle/_ref/libmps_ref.so; it solves the PPE twice per step, "
             "src/mps.cpp:457,460)" if kind == "reference" else "the oracle port (oracle/mps_oracle.cpp)")
-    return (f"{nsteps} step(s) of {what} on the same generator at nx_fluid={nx} ({n} particles); CG iterations "
-            f"grow ~1/l0, so the full-size CPU figure is lower still (see extrapolated_full_size)")
+    return (f"{nsteps} step(s) of {what} on the same generator at nx_fluid={nx} ({n} particles) - a REDUCED-SIZE "
+            f"sample: CG iterations grow with 1/l0, so CPU particle-steps/s at the full size is lower still "
+            f"(full_size_measured_once)")
+
+
+def full_size_cpu_record(nx):
+    """The reference timed ONCE at this size on the CPU (tests/golden/make_large_golden.py records the wall time of
+    every phase next to the parity fixture). The fixture times one solve; the reference performs two identical
+    ones per step (src/mps.cpp:457,460), so its step = 2 x solve + the other phases. Static, dated, not re-run."""
+    import numpy as np
+
+    path = os.path.join(ROOT, "tests", "golden", f"large_nx{nx}.npz")
+    if not os.path.exists(path):
+        return None
+    z = np.load(path)
+    sec = json.loads(str(z["seconds"]))
+    other = sum(v for k, v in sec.items() if k not in ("solve_once", "solve_reference_twice"))
+    step_s = 2.0 * sec["solve_once"] + other
+    n = int(z["n"])
+    return {"nx_fluid": int(z["nx"]), "particles": n, "seconds_per_reference_step": step_s,
+            "seconds_one_solve": sec["solve_once"], "cg_iterations": int(z["cg_iterations"]),
+            "value": n / step_s, "unit": UNIT, "cpu_model": str(z["cpu_model"]), "omp_threads": int(z["cpu_threads"]),
+            "when": str(z["when"]), "source": f"tests/golden/large_nx{nx}.npz (make_large_golden.py)",
+            "note": "measured once where the fixture was generated (not on this box, not in this run); the Eigen "
+                    "solve is serial, so the thread count only touches the ~4 % outside it"}
+
+
+def cpu_points(sizes, budget_s):
+    """The reference at several sizes with OMP_NUM_THREADS = 1 and all cores."""
+    allt = cpu_threads()
+    pts, kind = [], None
+    per = budget_s / max(1, 2 * len(sizes))
+    for nx in sizes:
+        for th in (1, allt):
+            kind, n, times = time_cpu_steps(nx, 3, 0, budget_s=per, threads=th)
+            sec = sum(times)
+            pts.append({"nx_fluid": nx, "particles": n, "threads": th, "steps": len(times),
+                        "ms_per_step": 1e3 * sec / len(times), "value": n * len(times) / sec})
+    set_omp_threads(allt)
+    return kind, pts
+
+
+CPU_MODEL_TEXT = ("reference step ~ 2 solves x iterations x (c1 nnz) + c2 n with iterations ~ nx^0.7-0.95 (999 / 1 912 / "
+                  "2 880 at nx = 400 / 800 / 1 416, profiles/r2_cpu_reference_scaling.json), so particle-steps/s "
+                  "FALLS with size; no extrapolated figure is reported as a measurement")
 
 
 def run_reference_arm(args):
@@ -155,11 +229,12 @@ def run_reference_arm(args):
     if rank != 0:
         return 0
     nx_cpu = args.cpu_nx
-    # keep the whole run within a few minutes: cost/step ~ 11 s * (nx/400)^3 on one core
+    # keep the whole run within a few minutes: cost/step ~ 8 s * (nx/400)^3 on one core (the solve is serial)
     total = max(1, args.steps + args.warmup)
-    while nx_cpu > 80 and 11.0 * (nx_cpu / 400.0) ** 3 * total > 240.0:
+    while nx_cpu > 80 and 8.0 * (nx_cpu / 400.0) ** 3 * total > 240.0:
         nx_cpu -= 40
-    kind, n, times = time_cpu_steps(nx_cpu, args.steps, args.warmup)
+    allt = cpu_threads()
+    kind, n, times = time_cpu_steps(nx_cpu, args.steps, args.warmup, threads=allt)
     from mps_b200 import cases as C
 
     n_full = len(C.scaled_dambreak(args.nx)[1])
@@ -169,15 +244,109 @@ def run_reference_arm(args):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": len(times), "warmup": args.warmup, "ms_per_step": 1e3 * sec / len(times), "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": workload_config(args.nx, n_full, "cpu"),
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cpu_threads(), "kind": kind,
+        # the size this line TIMED is nx_fluid_timed / particles_timed; nx_fluid / particles name the workload the
+        # b200 arm runs in full. A ratio of the two arms is therefore cross-size and a LOWER bound (see
+        # cpu_baseline.full_size_measured_once for the reference at the full size).
+        "config": workload_config(args.nx, n_full, "cpu", nx_timed=nx_cpu, n_timed=n),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": allt, "kind": kind, "cpu_model": cpu_model_name(),
                          "sample": cpu_sample_text(nx_cpu, n, kind, len(times)),
-                         "extrapolated_full_size": value * (nx_cpu / args.nx)},
+                         "nx_fluid_timed": nx_cpu, "particles_timed": n,
+                         "full_size_measured_once": full_size_cpu_record(args.nx), "size_model": CPU_MODEL_TEXT},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     _emit(out)
     return 0
+
+
+def other_configs(gpu_steps, with_cpu=True, cpu_seconds=1.5):
+    """BASELINE configs[0], [1], [2], [4] (the shipped, latency-bound sizes) through the same C ABI on this GPU,
+    beside the compiled reference on this box's cores with 1 thread and with all of them. Outside the timed
+    region of `value`. Returns a list of rows."""
+    import numpy as np
+
+    from mps_b200 import capi, cases as C
+    from oracle import refbind as R
+
+    rows = []
+    names = {"hydrostatic": "configs[0]", "dambreak": "configs[1]", "dambreak_fine": "configs[2]",
+             "dambreak_fine_original": "configs[4]"}
+    for case, cfg in names.items():
+        S, t, p, v = C.load_case(case)
+        n = int(np.count_nonzero(t != C.GHOST))
+        dev = capi.DeviceMPS(S, t, p, v)
+        dev.load_initial_state()
+        for _ in range(20):
+            dev.step_forward(False)
+        its, solve = [], []
+        t0 = time.perf_counter()
+        for _ in range(gpu_steps):
+            dev.step_forward(False)
+            st = dev.last_stats
+            its.append(st.cg_iterations)
+            solve.append(st.ms_solve)
+        wall = time.perf_counter() - t0
+        dev.close()
+        row = {"config": cfg, "case": case, "particles": n, "gpu_steps": gpu_steps,
+               "gpu_ms_per_step": 1e3 * wall / gpu_steps, "gpu_particle_steps_per_s": n * gpu_steps / wall,
+               "gpu_solve_ms_per_step": float(np.mean(solve)), "cg_iterations_per_step": float(np.mean(its)),
+               "gpu_us_per_cg_iteration": 1e3 * float(np.sum(solve)) / max(1, int(np.sum(its))),
+               "timing": "host wall clock around the C-ABI calls (one graph launch + stats read-back per step)"}
+        if with_cpu and R.have_ref():
+            yml, _ = C.case_paths(case)
+            for th in (1, cpu_threads()):
+                ref = R.RefMPS(yml, os.path.join(ROOT, S.input_csv_path))
+                set_omp_threads(th)
+                for _ in range(2):
+                    ref.step(False)
+                k, t0 = 0, time.perf_counter()
+                while time.perf_counter() - t0 < cpu_seconds:
+                    ref.step(False)
+                    k += 1
+                sec = time.perf_counter() - t0
+                ref.close()
+                row["cpu_ms_per_step_%s" % ("1_thread" if th == 1 else "all_threads")] = 1e3 * sec / k
+            row["cpu_threads_all"] = cpu_threads()
+            row["speedup_vs_best_cpu"] = min(row["cpu_ms_per_step_1_thread"], row["cpu_ms_per_step_all_threads"]) / row["gpu_ms_per_step"]
+        rows.append(row)
+    return rows
+
+
+def parity_vs_one_gpu(dev, S, t, p, v, local, world):
+    """N > 1: one step from the initial state on the N-rank handle and on a single-GPU handle of the same
+    library on this rank's device. Returns the block for the JSON line; `ok` False fails the run."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    from mps_b200 import capi
+
+    single = capi.DeviceMPS(S, t, p, v, device=local)
+    single.load_initial_state()
+    single.step_forward(True)
+    dev.step_forward(True)
+    a, b = dev.download(), single.download()
+    it = (dev.last_stats.cg_iterations, single.last_stats.cg_iterations)
+    single.close()
+    dev.upload({"type": t, "position": p, "velocity": v})  # the timed steps start from the initial state at every N
+    dev.load_initial_state()
+    flags = bool(np.array_equal(a["type"], b["type"]) and np.array_equal(a["boundary_condition"], b["boundary_condition"]))
+    worst = {}
+    for name in ("pressure", "velocity", "position", "number_density_ratio"):
+        scale = max(float(np.abs(b[name]).max()), 1e-300)
+        worst[name] = float(np.abs(a[name] - b[name]).max()) / scale
+    mine = torch.from_numpy(np.concatenate([a["pressure"], a["velocity"].ravel(), a["position"].ravel()])).cuda()
+    ref = mine.clone()
+    dist.broadcast(ref, src=0)
+    same = torch.tensor([int(torch.equal(mine.view(torch.int64), ref.view(torch.int64)))], device="cuda")
+    dist.all_reduce(same, op=dist.ReduceOp.MIN)
+    ok = bool(same.item()) and flags and all(x <= 1e-10 for x in worst.values())
+    okt = torch.tensor([int(ok)], device="cuda")
+    dist.all_reduce(okt, op=dist.ReduceOp.MIN)
+    return {"ok": bool(okt.item()), "ranks_bit_identical": bool(same.item()), "flags_equal": flags, "max_rel": worst,
+            "cg_iterations_n_gpus_vs_1": list(it), "tolerance": 1e-10,
+            "how": "one step from the initial state; N-rank handle vs a single-GPU handle of the same library on "
+                   "every rank's own device; the single-GPU path is pinned to the reference by the -m gpu tests"}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -208,6 +377,9 @@ def run_gpu_arm(args):
     stream = torch.cuda.current_stream()
     dev.set_stream(stream.cuda_stream)
     dev.load_initial_state()
+    parity = None
+    if world > 1 and not args.no_parity:
+        parity = parity_vs_one_gpu(dev, S, t, p, v, local, world)
 
     def barrier():
         if world > 1:
@@ -232,6 +404,7 @@ def run_gpu_arm(args):
     barrier()
     ms = e0.elapsed_time(e1)
     launches = dev.launch_count - launches0
+    cyc = dev.cg_cycles()  # CTA 0 of this rank, last solve: SM cycles in sweep A / B / C / barriers+reductions(+exchanges)
     clocks = sampler.stop() if rank == 0 else None
     if world > 1:
         tms = torch.tensor([ms], device="cuda", dtype=torch.float64)
@@ -303,11 +476,18 @@ def run_gpu_arm(args):
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        kind, n, times = time_cpu_steps(args.cpu_nx, 3, 0, budget_s=10.0)
-        v_cpu = n * len(times) / sum(times)
-        cpu = {"value": v_cpu, "unit": UNIT, "cores": cpu_threads(), "kind": kind,
-               "sample": cpu_sample_text(args.cpu_nx, n, kind, len(times)),
-               "extrapolated_full_size": v_cpu * (args.cpu_nx / args.nx)}
+        # bounded sample (~20 s): two sizes x {1 thread, all cores}; `value` is the larger size with all cores
+        sizes = sorted({max(80, args.cpu_nx // 2), args.cpu_nx})
+        kind, pts = cpu_points(sizes, budget_s=20.0)
+        head = [q for q in pts if q["nx_fluid"] == args.cpu_nx and q["threads"] == cpu_threads()][0]
+        cpu = {"value": head["value"], "unit": UNIT, "cores": cpu_threads(), "kind": kind, "cpu_model": cpu_model_name(),
+               "sample": cpu_sample_text(args.cpu_nx, head["particles"], kind, head["steps"]),
+               "nx_fluid_timed": args.cpu_nx, "particles_timed": head["particles"], "points": pts,
+               "full_size_measured_once": full_size_cpu_record(args.nx), "size_model": CPU_MODEL_TEXT}
+
+    other = None
+    if rank == 0 and world == 1 and not args.no_other:
+        other = other_configs(args.other_steps, with_cpu=not args.no_cpu)
 
     if rank == 0:
         out = {
@@ -320,12 +500,20 @@ def run_gpu_arm(args):
             "phase_ms_per_step": {k[3:]: mean(k) for k in ("ms_neighbors", "ms_explicit", "ms_collision", "ms_assemble",
                                                            "ms_solve", "ms_correct", "ms_total")},
             "n_inner": stats[-1]["n_inner"], "nnz": stats[-1]["nnz"],
+            "cg_cycle_split": {"A_spmv": cyc[0] / max(1, sum(cyc)), "B_update": cyc[1] / max(1, sum(cyc)),
+                               "C_direction": cyc[2] / max(1, sum(cyc)), "sync": cyc[3] / max(1, sum(cyc)),
+                               "of": "rank 0, CTA 0, last solve (SM cycles)"},
+            "sync_us_per_iteration": (cyc[3] / max(1, sum(cyc))) * 1e3 * solve_ms / max(1, sum(s["cg_iterations"] for s in stats)),
+            "parity_vs_1gpu": parity, "other_configs": other,
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
         }
         _emit(out)
     dev.close()
     if world > 1:
         torch.distributed.destroy_process_group()
+    if parity is not None and not parity["ok"]:
+        sys.stderr.write("bench.py: N-GPU result differs from one GPU beyond 1e-10: %s\n" % json.dumps(parity))
+        return 3
     return 0
 
 
@@ -365,6 +553,9 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-other", action="store_true", help="skip the other_configs block (BASELINE configs 0, 1, 2, 4)")
+    ap.add_argument("--other-steps", type=int, default=200)
+    ap.add_argument("--no-parity", action="store_true", help="N > 1: skip the one-step parity check against one GPU")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference_arm(args)

@@ -15,6 +15,8 @@
  *                                32 768; 0 = always the multi-launch radix sort)
  *   MPSB_FORCE_WIDE_COLUMNS=1    stream int32 PPE columns even when 16-bit offsets fit
  *   MPSB_CG_ITERATION_CAP=<n>    stop the solve after n iterations (profiling a bounded solve)
+ *   MPSB_MATRIX_FREE=0|1         sweep A of the grid solve streams the stored off-diagonals (0) or recomputes them from
+ *                                positions (1; 2-D cases only)
  * and by the host mirror (mps_b200/host): MPSB_DEVICE=<ordinal>, MPSB_CSV_FLOAT=gcc5.
  *
  * Particle arrays are SoA, indexed by particle id (the reference assumes id == index,
@@ -97,6 +99,7 @@ typedef struct mpsb_step_stats {
     int32_t courant_exceeds_cfl; /* 1 if courant > cfl_condition (debugLogCount += ) */
     int32_t ppe_columns_16bit;   /* 1: the solve streamed 16-bit column offsets (10 B per entry), 0: int32 columns (12 B) */
     int32_t solve_in_cluster;    /* 1: the small-system cluster kernel did the solve (k_pcg_cluster.cu), 0: the grid kernel */
+    int32_t ppe_matrix_free;     /* 1: sweep A of the solve recomputed the off-diagonals from positions (2 B per entry streamed) */
 } mpsb_step_stats;
 
 typedef struct mpsb_handle mpsb_handle;
@@ -202,6 +205,10 @@ int mpsb_debug_cg_cycles(const mpsb_handle* h, int64_t* out4);
 /* Diagnostic: the same four counters for every CTA of the last solve plus its SM id, as 5 rows of
  * *nblocks int64 (row-major: A, B, C, sync, smid). */
 int mpsb_debug_cg_block_cycles(mpsb_handle* h, int64_t* out, int capacity_blocks, int* nblocks);
+/* Diagnostic / parity: y = A x with the PPE of the last MATRIX/DIRICHLET phase, x and y host vectors indexed by
+ * particle id (entries of non-Inner particles ignored / returned 0). matrix_free = 0 applies the stored entries,
+ * 1 the recomputation from positions the solve uses in matrix-free mode. Single GPU only. */
+int mpsb_debug_spmv(mpsb_handle* h, const double* x, double* y, int matrix_free);
 /* Counters since create: kernel launches issued by this library on this handle. */
 int64_t mpsb_launch_count(const mpsb_handle* h);
 

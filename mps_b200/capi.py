@@ -27,7 +27,7 @@ EXPORTED = [
     "mpsb_create", "mpsb_destroy", "mpsb_last_error", "mpsb_version", "mpsb_step", "mpsb_run_phase",
     "mpsb_upload", "mpsb_download", "mpsb_num_particles", "mpsb_get_neighbors", "mpsb_get_ppe", "mpsb_events",
     "mpsb_comm_unique_id", "mpsb_attach_comm", "mpsb_upload_device", "mpsb_launch_count", "mpsb_set_stream",
-    "mpsb_debug_cg_cycles", "mpsb_debug_cg_block_cycles",
+    "mpsb_debug_cg_cycles", "mpsb_debug_cg_block_cycles", "mpsb_debug_spmv",
 ]
 
 
@@ -39,6 +39,7 @@ class CStepStats(ct.Structure):
         ("cg_iterations", ct.c_int32), ("n_active", ct.c_int32), ("n_inner", ct.c_int32), ("n_surface", ct.c_int32),
         ("nnz", ct.c_int32), ("n_ghosted", ct.c_int32), ("n_unconnected", ct.c_int32), ("n_collisions", ct.c_int32),
         ("max_neighbors", ct.c_int32), ("courant_exceeds_cfl", ct.c_int32), ("ppe_columns_16bit", ct.c_int32), ("solve_in_cluster", ct.c_int32),
+        ("ppe_matrix_free", ct.c_int32),
     ]
 
     def as_dict(self):
@@ -301,6 +302,15 @@ class DeviceMPS:
         flat = np.zeros(5 * cap, dtype=np.int64)
         self._check(self.lib.mpsb_debug_cg_block_cycles(self.h, flat.ctypes.data, cap, ct.byref(nb)))
         return flat[:5 * nb.value].reshape(5, nb.value)
+
+    def spmv(self, x, matrix_free):
+        """y = A x with the last assembled PPE (vectors by particle id); stored entries or the matrix-free operator."""
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        y = np.zeros_like(x)
+        self.lib.mpsb_debug_spmv.restype = ct.c_int
+        self.lib.mpsb_debug_spmv.argtypes = [ct.c_void_p, ct.c_void_p, ct.c_void_p, ct.c_int]
+        self._check(self.lib.mpsb_debug_spmv(self.h, x.ctypes.data, y.ctypes.data, int(matrix_free)))
+        return y
 
     @property
     def launch_count(self):

@@ -310,6 +310,25 @@ def scaled_dambreak(nx_fluid: int, base: str = "dambreak_fine"):
     return s, t, p, np.zeros_like(p)
 
 
+def jittered(s: Settings, types, pos, seed: int, amplitude: float = 0.1):
+    """A mid-flow-like 2-D state for parity fixtures that cannot carry a state (tests/golden/large_*):
+    fluid positions moved by a seeded uniform jitter of +-amplitude*l0 in x and y, fluid velocities from a
+    polynomial field. Only +, -, * on doubles and numpy's PCG64 stream, so every machine regenerates the
+    same bits from (nx, seed). Minimum distance stays (1 - 2*amplitude)*l0, above the collision distance."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    fluid = types == FLUID
+    l0 = s.particle_distance
+    p = pos.copy()
+    d = (rng.random((len(types), 2)) - 0.5) * (2.0 * amplitude * l0)
+    p[fluid, 0] += d[fluid, 0]
+    p[fluid, 1] += d[fluid, 1]
+    v = np.zeros_like(p)
+    x, y = p[:, 0], p[:, 1]
+    v[fluid, 0] = (0.3 * (x * (1.0 - x)) * (y - 0.3))[fluid]
+    v[fluid, 1] = (-0.2 * (x * y))[fluid]
+    return p, v
+
+
 def write_settings_yaml(s: Settings, path: str, finish_time=None, output_interval=None):
     """settings.yml with the reference's exact keys (src/settings.cpp:20-84) for a generated case, so the
     compiled reference (whose MPS constructor only takes a YAML path) can run the same settings.

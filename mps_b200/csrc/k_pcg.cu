@@ -65,6 +65,9 @@ namespace cg = cooperative_groups;
 #ifndef PCG_VEC_HINT
 #define PCG_VEC_HINT 0 // 1: L2 evict_last policy on the p / ap / r accesses of sweeps B and C
 #endif
+#ifndef MPSB_MATRIX_FREE_DEFAULT
+#define MPSB_MATRIX_FREE_DEFAULT 0 // sweep A recomputes off-diagonals from positions (see spmv_sweep_mf); env MPSB_MATRIX_FREE overrides
+#endif
 #ifndef PCG_SPLIT_SYNC
 #define PCG_SPLIT_SYNC 0 // diagnostic: book the barrier/exchange after sweep B under B and after sweep C under C
 #endif
@@ -515,9 +518,164 @@ bulk_g2s(S.val, P.ell_val + off, (unsigned) nsl * 256u, bar);
     }
 }
 
+
+// ---- matrix-free sweep A (2-D) -------------------------------------------------------------------------
+// The stored sweep streams 10 B per off-diagonal (fp64 value + 16-bit column) and sits at the HBM roof for
+// that format (frac 0.99). Every off-diagonal is a function of one distance,
+//     a_ij = -(mat_coef / density) * (re_p / d_ij - 1)             (src/mps.cpp:343-349)
+// so this sweep streams only the 2-byte column and RECOMPUTES the value from the two positions: one 16-byte
+// gather of (x_j, y_j) next to the 8-byte gather of p_j (both L1/L2-resident: SORTED order keeps a row's
+// neighbours within +-1 cell row), 11 fp64 operations per entry on the otherwise idle FP64 pipe:
+//     q   = (x_j - x_i)^2 + (y_j - y_i)^2                          differences of the stored doubles
+//     z0  = rsqrt.approx(q)                                         MUFU.RSQ64H, ~22 bits of 1/d
+//     z   = z0 + z0 e (1/2 + 3/8 e),  e = 1 - q z0^2               one third-order step: 22 -> ~64 bits
+//     acc += (re z - 1) p_j
+//     ap_i = diag_i p_i - (mat_coef / density) * acc
+// The diagonal (which also carries the quasi-compressibility term and the Dirichlet doubling) stays stored.
+// Entries differ from the assembled ones (which mpsb_get_ppe still returns bit-exactly) by a few ulp: the
+// contract on matrix entries is 1e-10 relative (north_star), on the pressure 1e-10; both are tested. The
+// operator stays exactly symmetric: (x_j - x_i)^2 == (x_i - x_j)^2 bit for bit.
+// One ring stage holds the columns of up to MF_CH slots (the `val` area of a Stage reinterpreted), so a
+// slice is normally ONE bulk copy of width * 64 B + its 256 B of diagonals.
+constexpr int MF_CH = (PCG_CH * 256) / 64; // 16-bit column slots that fit the value area of a stage (48)
+constexpr int MF_G  = 8;                    // entries whose gathers are in flight together
+
+__device__ __forceinline__ double mf_weight(double dx, double dy, double re) {
+    const double q = fma(dy, dy, dx * dx); // d^2
+    double z;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(z) : "d"(q)); // MUFU.RSQ64H: ~22 bits of 1/d
+    const double t  = z * z;
+    const double e  = fma(-q, t, 1.0);
+    const double g  = fma(0.375, e, 0.5);
+    const double ge = g * e;
+    z = fma(z, ge, z);      // third-order step: 1/d to ~1 ulp
+    return fma(re, z, -1.0); // re / d - 1
+}
+
+__device__ __forceinline__ void spmv_sweep_mf(const Params& P, Smem& sm, Pipe& pipe, int sbeg, int nslices, const double* p,
+                                              double* ap, unsigned* ticket, double* slice_pap, const HaloWait& hw) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const size_t K = (size_t) P.K;
+    const int nsl_total = nslices - sbeg;
+    const double re = P.s.re_pressure;
+    const double neg_coef = -(P.mat_coef / P.s.density);
+    const double2* xy = P.row_xy;
+    auto rot = [&](int v) -> int {
+        int x = v - sbeg + hw.shift;
+        if (x >= nsl_total) x -= nsl_total;
+        return sbeg + x;
+    };
+    bool halo_ready = false;
+    auto take = [&]() -> int {
+        int v = 0;
+        if (lane == 0) v = sbeg + (int) atomicAdd(ticket, (unsigned) PCG_BATCH);
+        return v;
+    };
+    auto widths = [&](int s0) -> int { return (lane < PCG_BATCH && s0 + lane < nslices) ? P.ell_width[rot(s0 + lane)] : 0; };
+    int cur = __shfl_sync(0xffffffffu, take(), 0);
+    int cur_w = widths(cur);
+    int nxt = __shfl_sync(0xffffffffu, take(), 0);
+    int nxt_w = widths(nxt);
+    int t2 = take();
+    int pi = 0, pk = 0;
+    int pw = __shfl_sync(0xffffffffu, cur_w, 0);
+    auto produce = [&]() -> bool {
+        if (cur + pi >= nslices || pipe.issued - pipe.consumed >= (unsigned) PCG_STAGES) return false;
+        const int slice = rot(cur + pi);
+        const int nsl   = min(MF_CH, pw - pk);
+        const int halo  = (slice < hw.gap_lo || slice >= hw.gap_hi) ? 2 : 0;
+        const bool first = pk == 0, last = pk + nsl >= pw;
+        const unsigned st = pipe.issued % PCG_STAGES;
+        if (lane == 0) {
+            Stage& S = sm.stage[warp][st];
+            sm.meta[warp][st] = StageMeta{slice, nsl, (first ? 1 : 0) | halo | (pk << 8), last ? 1 : 0};
+            unsigned long long* bar = &sm.full[warp][st];
+            mbar_arrive_expect_tx(bar, (first ? 256u : 0u) + (unsigned) nsl * 64u);
+            if (first) bulk_g2s(S.diag, P.diag + (size_t) slice * 32, 256u, bar);
+            if (nsl > 0) bulk_g2s(S.val, P.ell_col16 + ((size_t) slice * K + (size_t) pk) * 32, (unsigned) nsl * 64u, bar);
+        }
+        pipe.issued++;
+        pk += nsl;
+        if (last) {
+            pk = 0;
+            if (++pi == PCG_BATCH) {
+                pi = 0;
+                cur = nxt; cur_w = nxt_w;
+                nxt = __shfl_sync(0xffffffffu, t2, 0);
+                nxt_w = widths(nxt);
+                t2 = nxt < nslices ? take() : nslices;
+            }
+            pw = __shfl_sync(0xffffffffu, cur_w, pi);
+        }
+        return true;
+    };
+    double acc = 0.0, pr = 0.0, dpr = 0.0;
+    double2 me = make_double2(0.0, 0.0);
+    int row = 0, cnt = 0;
+    for (;;) {
+        while (produce()) {}
+        if (pipe.consumed == pipe.issued) break;
+        __syncwarp();
+        const unsigned st = pipe.consumed % PCG_STAGES, parity = (pipe.consumed / PCG_STAGES) & 1u;
+        const StageMeta m = sm.meta[warp][st];
+        const Stage& S    = sm.stage[warp][st];
+        if (m.first & 1) { // own-row loads: issued before the wait so their latency hides behind the TMA
+            row = m.slice * 32 + lane;
+            pr  = p[row];
+            me  = xy[row];
+            cnt = P.ell_count[row];
+        }
+        mbar_wait(&sm.full[warp][st], parity);
+        if ((m.first & 2) && !halo_ready) {
+            if (lane == 0) {
+                const unsigned long long t0 = global_timer_ns();
+                unsigned spins = 0;
+                for (int q = 0; q < hw.world; q++)
+                    while (ld_acquire_sys(hw.flags + q) < hw.epoch)
+                        if ((++spins & 1023u) == 0) xchg_timeout(P, t0);
+            }
+            __syncwarp();
+            halo_ready = true;
+        }
+        if (m.first & 1) {
+            dpr = S.diag[lane] * pr;
+            acc = 0.0;
+        }
+        const short* c16 = reinterpret_cast<const short*>(S.val);
+        const int base = m.slice * 32, k0 = m.first >> 8;
+#pragma unroll 1
+        for (int k = 0; k < m.nslots; k += MF_G) { // nslots is a multiple of 4: the second half of a group may be absent
+            double2 q[MF_G];
+            double g[MF_G];
+#pragma unroll
+            for (int b = 0; b < MF_G; b++) {
+                const int c = (k + b < m.nslots) ? base + (int) c16[(k + b) * 32 + lane] : row;
+                q[b] = xy[c];
+                g[b] = p[c];
+            }
+#pragma unroll
+            for (int b = 0; b < MF_G; b++) {
+                const double w = mf_weight(q[b].x - me.x, q[b].y - me.y, re);
+                // padding slots (column = own row, d = 0 -> w = inf/NaN) and absent ones are selected away, not multiplied
+                acc = fma((k0 + k + b < cnt) ? w : 0.0, g[b], acc);
+            }
+        }
+        if (m.last) {
+            const double sum = fma(neg_coef, acc, dpr);
+            ap[row] = sum;
+            double v = pr * sum;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            if (lane == 0) slice_pap[m.slice] = v;
+        }
+        __syncwarp();
+        pipe.consumed++;
+    }
+}
+
 // MULTI = false: one GPU, rows [0, n). MULTI = true: this rank's row block; see the file header.
 template <bool MULTI>
-__global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_blocks, int iteration_cap) {
+__global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_blocks, int iteration_cap, int matrix_free) {
     if (*P.cluster_done) { // the cluster solve (k_pcg_cluster.cu) already did it; uniform over the grid
         if (blockIdx.x == 0 && threadIdx.x == 0) *P.ell_wide = 0; // consumed: the next assembly starts from "fits"
         return;
@@ -669,7 +827,8 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
         // ---- sweep A: ap = A p, p.ap ----
         unsigned* ticket = tickets + (it & 1);
         if (MULTI) hw.epoch = halo_epoch;
-        if (col16) spmv_sweep<true>(P, sm, pipe, sl_lo, sl_hi, p, ap, ticket, P.cg_slice_pap, hw);
+        if (col16 && matrix_free) spmv_sweep_mf(P, sm, pipe, sl_lo, sl_hi, p, ap, ticket, P.cg_slice_pap, hw);
+        else if (col16) spmv_sweep<true>(P, sm, pipe, sl_lo, sl_hi, p, ap, ticket, P.cg_slice_pap, hw);
         else spmv_sweep<false>(P, sm, pipe, sl_lo, sl_hi, p, ap, ticket, P.cg_slice_pap, hw);
         __syncthreads();
         PCG_TICK(0);
@@ -780,7 +939,7 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
         for (int k = 0; k < 4; k++) P.stats->cg_cycles[k] = cyc[k];
         P.stats->cg_iterations   = it;
         P.stats->pad[0]          = col16 ? 1 : 0;
-        P.stats->pad[1]          = 0;
+        P.stats->pad[1]          = (col16 && matrix_free) ? 2 : 0; // bit 1: sweep A recomputed the off-diagonals
         // leave the launch-scoped scratch cleared for the next solve (saves memset nodes): the two slice-queue
         // counters (no sweep A is running any more) and the column-width flag of the assembly just consumed
         tickets[0] = 0u;
@@ -793,12 +952,33 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
     }
 }
 
+
+// Diagnostic / parity: ONE sweep A (y = A x over the SORTED rows of the assembled system) outside the solve, on
+// the stored stream or on the matrix-free recomputation, so tests can compare the two operators entry by entry
+// (unit vectors) and on random vectors. x lives in cg_p, y in cg_ap; single GPU only.
+__global__ void __launch_bounds__(PCG_THREADS, 1) spmv_probe_kernel(Params P, int max_blocks, int matrix_free) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    Smem& sm = *reinterpret_cast<Smem*>(smem_raw);
+    if (threadIdx.x < PCG_WARPS * PCG_STAGES) mbar_init(&sm.full[0][0] + threadIdx.x, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    __syncthreads();
+    Pipe pipe{0u, 0u};
+    const int n = *P.n_active, sl_hi = (n + 31) >> 5;
+    unsigned* tickets = reinterpret_cast<unsigned*>(P.cg_partials + 8 * (size_t) max_blocks);
+    HaloWait hw{0, 0, sl_hi, nullptr, 0ull, 1};
+    const bool col16 = *P.ell_wide == 0;
+    if (col16 && matrix_free) spmv_sweep_mf(P, sm, pipe, 0, sl_hi, P.cg_p, P.cg_ap, tickets, P.cg_slice_pap, hw);
+    else if (col16) spmv_sweep<true>(P, sm, pipe, 0, sl_hi, P.cg_p, P.cg_ap, tickets, P.cg_slice_pap, hw);
+    else spmv_sweep<false>(P, sm, pipe, 0, sl_hi, P.cg_p, P.cg_ap, tickets, P.cg_slice_pap, hw);
+}
+
 } // namespace
 
 int mpsb_pcg_configure(mpsb_handle* h) {
     int smem = (int) sizeof(Smem);
     if (cudaFuncSetAttribute(pcg_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return -1;
     if (cudaFuncSetAttribute(pcg_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return -1;
+    if (cudaFuncSetAttribute(spmv_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return -1;
     int per_sm = 0;
     cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, pcg_kernel<true>, PCG_THREADS, smem);
     if (e != cudaSuccess || per_sm < 1) return -1;
@@ -807,6 +987,10 @@ int mpsb_pcg_configure(mpsb_handle* h) {
     h->cg_max_blocks = h->num_sms; // one CTA per SM
     const char* cap  = getenv("MPSB_CG_ITERATION_CAP"); // diagnostic (profiling a bounded solve); 0 = Eigen's 2N
     h->cg_iteration_cap = cap ? atoi(cap) : 0;
+    // matrix-free sweep A: 2-D cases with a flat z (all particles in one plane) only; MPSB_MATRIX_FREE=0/1 overrides
+    const mpsb_settings& s = h->P.s;
+    const char* mf = getenv("MPSB_MATRIX_FREE");
+    h->cg_matrix_free = (s.dim == 2 && s.domain_max[2] == s.domain_min[2]) ? (mf ? (atoi(mf) ? 1 : 0) : MPSB_MATRIX_FREE_DEFAULT) : 0;
     return 0;
 }
 
@@ -821,8 +1005,21 @@ void mpsb_launch_pcg(mpsb_handle* h) {
     int max_blocks = h->cg_max_blocks;
     if (multi) cudaMemsetAsync(P.L.arrive, 0, 2 * sizeof(unsigned long long), h->stream); // both arrival counters
     int cap = h->cg_iteration_cap;
-    void* args[] = {(void*) &P, (void*) &max_blocks, (void*) &cap};
+    int mfree = h->cg_matrix_free;
+    void* args[] = {(void*) &P, (void*) &max_blocks, (void*) &cap, (void*) &mfree};
     const void* fn = multi ? (const void*) pcg_kernel<true> : (const void*) pcg_kernel<false>;
     cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(PCG_THREADS), args, (size_t) h->cg_smem, h->stream);
     h->launches++;
+}
+
+// y = A x for the last assembled PPE; x and y are DEVICE vectors over SORTED rows already placed in cg_p / read from
+// cg_ap by the caller (mpsb_debug_spmv, mpsb_api.cu).
+void mpsb_launch_spmv_probe(mpsb_handle* h, int matrix_free) {
+    Params& P = h->P;
+    int grid = mpsb_div_up(P.Np / 32, PCG_WARPS);
+    if (grid > h->cg_max_blocks) grid = h->cg_max_blocks;
+    if (grid < 1) grid = 1;
+    cudaMemsetAsync(P.cg_partials + 8 * (size_t) h->cg_max_blocks, 0, 2 * sizeof(double), h->stream); // slice-queue counters
+    MPSB_LAUNCH(h, spmv_probe_kernel, grid, PCG_THREADS, (size_t) h->cg_smem, P, h->cg_max_blocks, matrix_free);
+    cudaMemsetAsync(P.cg_partials + 8 * (size_t) h->cg_max_blocks, 0, 2 * sizeof(double), h->stream);
 }

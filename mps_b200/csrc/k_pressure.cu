@@ -130,6 +130,7 @@ __global__ void __launch_bounds__(256) matrix_kernel(Params P, int force_wide) {
     }
     P.ell_count[s] = m;
     P.diag[s]      = diag;
+    P.row_xy[s]    = make_double2(P.S.x[s], P.S.y[s]); // rows >= N: zero-filled allocation, never a column
 }
 
 // ---- Dirichlet connectivity ------------------------------------------------------------------------

@@ -92,7 +92,8 @@ void fill_stats(mpsb_handle* h, mpsb_step_stats* st) {
     st->n_collisions    = d.n_collisions;
     st->max_neighbors   = d.max_neighbors;
     st->ppe_columns_16bit = d.pad[0];
-    st->solve_in_cluster  = d.pad[1];
+    st->solve_in_cluster  = d.pad[1] & 1;
+    st->ppe_matrix_free   = (d.pad[1] >> 1) & 1;
     st->courant_exceeds_cfl = d.courant_bits_as_double > h->P.s.cfl_condition;
 }
 
@@ -207,6 +208,7 @@ int mpsb_create(const mpsb_settings* settings, int64_t n, const int32_t* type, c
     CKC(dalloc(&P.cg_partials, 8 * (size_t) h->cg_max_blocks + 8));
     CKC(dalloc(&P.cg_slice_pap, N / 32 + 1));
     CKC(dalloc(&P.cluster_done, 1));
+    CKC(dalloc(&P.row_xy, N));
     mpsb_pcg_cluster_configure(h); // optional fast path for small systems; 0 = this device cannot co-schedule a cluster
     {
         const char* nc = getenv("MPSB_NO_CLUSTER_SOLVE");
@@ -244,7 +246,7 @@ int mpsb_destroy(mpsb_handle* h) {
     void* ptrs[] = {S.x, S.y, S.z, S.u, S.v, S.w, S.u2, S.v2, S.w2, S.ax, S.ay, S.az, S.p, S.minp, S.ratio, S.type,
                     S.bc, S.id, H.pos, H.vel, H.acc, H.p, H.minp, H.ratio, H.type, H.bc, H.inv, P.key, P.key_alt,
                     P.val, P.val_alt, P.cell_start, P.cell_end, P.nbr_count, P.nbr_idx, P.nbr_dist, P.ell_count,
-                    P.ell_width, P.ell_cmin, P.ell_cmax, P.ell_col, P.ell_col16, P.ell_wide, P.ell_val, P.diag, P.rhs, P.cg_r, P.cg_p, P.cg_ap, P.cg_invdiag, P.cg_partials, P.cg_slice_pap, P.cluster_done,
+                    P.ell_width, P.ell_cmin, P.ell_cmax, P.ell_col, P.ell_col16, P.ell_wide, P.ell_val, P.diag, P.rhs, P.cg_r, P.cg_p, P.cg_ap, P.cg_invdiag, P.cg_partials, P.cg_slice_pap, P.cluster_done, P.row_xy,
                     P.parent, P.mark, P.cand, P.cand_count, P.ev_ghost_id, P.ev_ghost_xyz, P.ev_uncon_id, P.stats,
                     h->block_hist};
     for (void* p : ptrs)
@@ -600,6 +602,33 @@ int mpsb_debug_cg_block_cycles(mpsb_handle* h, int64_t* out, int capacity_blocks
     *nblocks = mb;
     if (capacity_blocks < mb) return MPSB_ERR_CAPACITY;
     CK(h, cudaMemcpy(out, h->P.cg_partials + 3 * (size_t) mb, sizeof(int64_t) * 5 * (size_t) mb, cudaMemcpyDeviceToHost));
+    return MPSB_OK;
+}
+
+// Diagnostic / parity: y = A x with the PPE of the last MATRIX/DIRICHLET phase, x and y indexed by particle id
+// (entries of non-Inner particles are ignored / returned as 0). matrix_free = 0: the stored sliced-ELL stream;
+// 1: the recomputation from positions that the solve uses in matrix-free mode (k_pcg.cu spmv_sweep_mf).
+int mpsb_debug_spmv(mpsb_handle* h, const double* x, double* y, int matrix_free) {
+    if (!h || !x || !y) return MPSB_ERR_ARG;
+    if (h->sticky) return h->sticky;
+    if (h->world > 1) return MPSB_ERR_ARG;
+    CK(h, cudaSetDevice(h->device));
+    const Params& P = h->P;
+    size_t N = (size_t) P.N;
+    std::vector<int> inv(N), bc(N);
+    CK(h, cudaStreamSynchronize(h->stream));
+    CK(h, cudaMemcpy(inv.data(), P.H.inv, sizeof(int) * N, cudaMemcpyDeviceToHost));
+    CK(h, cudaMemcpy(bc.data(), P.S.bc, sizeof(int) * N, cudaMemcpyDeviceToHost));
+    std::vector<double> xs((size_t) P.Np, 0.0), ys((size_t) P.Np, 0.0);
+    for (size_t i = 0; i < N; i++)
+        if (bc[(size_t) inv[i]] == MPSB_BC_INNER) xs[(size_t) inv[i]] = x[i];
+    CK(h, cudaMemcpy(P.cg_p, xs.data(), sizeof(double) * (size_t) P.Np, cudaMemcpyHostToDevice));
+    CK(h, cudaMemset(P.cg_ap, 0, sizeof(double) * (size_t) P.Np));
+    mpsb_launch_spmv_probe(h, matrix_free ? 1 : 0);
+    CK(h, cudaStreamSynchronize(h->stream));
+    CK(h, cudaGetLastError());
+    CK(h, cudaMemcpy(ys.data(), P.cg_ap, sizeof(double) * (size_t) P.Np, cudaMemcpyDeviceToHost));
+    for (size_t i = 0; i < N; i++) y[i] = bc[(size_t) inv[i]] == MPSB_BC_INNER ? ys[(size_t) inv[i]] : 0.0;
     return MPSB_OK;
 }
 

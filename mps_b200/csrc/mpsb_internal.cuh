@@ -116,6 +116,8 @@ struct Params {
     double *cg_r, *cg_p, *cg_ap, *cg_invdiag; // N
     double *cg_partials;       // 8 * max_blocks + 1: 3 reduction rows, 5 diagnostic rows, 2 slice-queue counters
     double *cg_slice_pap;      // Np/32 + 1: p.Ap of each 32-row slice (deterministic two-level sum)
+    double2 *row_xy;           // Np: (x, y) of every SORTED row as one 16-byte record, written by the assembly for the
+                               // matrix-free sweep A (k_pcg.cu): off-diagonals are recomputed from positions
     int *cluster_done;         // 1     set by the cluster solve (k_pcg_cluster.cu) when it did the solve
     // Dirichlet connectivity
     int *parent;               // N
@@ -153,6 +155,7 @@ struct mpsb_handle {
     int cg_threads;
     int cg_smem;            // dynamic shared memory of the PCG kernel
     int cg_iteration_cap;   // diagnostic: stop the solve after this many iterations (0 = Eigen's 2N)
+    int cg_matrix_free;     // sweep A recomputes the off-diagonals from positions instead of streaming them (2-D; MPSB_MATRIX_FREE)
     int num_sms;
     int cl_size, cl_smem;   // cluster solve for small systems (k_pcg_cluster.cu): cluster size (0 = unavailable), dynamic smem
     int cl_launched;        // the cluster kernel has run on this handle (*cluster_done may be set)
@@ -189,6 +192,7 @@ void mpsb_launch_dirichlet(mpsb_handle* h);
 void mpsb_launch_pressure_post(mpsb_handle* h);
 void mpsb_launch_pcg(mpsb_handle* h);                   // k_pcg.cu
 int mpsb_pcg_configure(mpsb_handle* h);
+void mpsb_launch_spmv_probe(mpsb_handle* h, int matrix_free); // diagnostic: one sweep A, cg_p -> cg_ap
 int mpsb_pcg_cluster_configure(mpsb_handle* h);         // k_pcg_cluster.cu
 int mpsb_launch_pcg_cluster(mpsb_handle* h);
 int mpsb_comm_gather_pressure(mpsb_handle* h);          // mpsb_comm.cu: all-gather the solved row blocks of p

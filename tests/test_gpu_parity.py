@@ -77,7 +77,8 @@ def test_phases_teacher_forced(path):
             assert np.array_equal(d[0], z["ppe_row_start"]) and np.array_equal(d[2], z["ppe_val"])
         if name == "solve":
             assert U.rel_err(a["pressure"], b["pressure"]) <= TOL, where
-            assert abs(st.cg_iterations - int(z["cg_iterations"])) <= 2 + int(z["cg_iterations"]) // 10  # +-10 % near the eps floor
+            assert abs(st.cg_iterations - int(z["cg_iterations"])) <= max(2, 0.02 * int(z["cg_iterations"]))  # observed: < 1 %
+            assert U.elementwise_excess(a["pressure"], b["pressure"], TOL) <= 1.0, where
             assert st.cg_rel_residual <= 2.3e-16
             assert_state_bitwise(a, b, where, skip=("pressure",))
             dev.upload({"pressure": b["pressure"]})
@@ -102,6 +103,7 @@ def test_step_teacher_forced(path):
     live = after["type"] != C.GHOST
     for name in ("position", "velocity", "pressure", "minimum_pressure", "acceleration"):
         assert U.rel_err(got[name], after[name]) <= TOL, name
+        assert U.elementwise_excess(got[name], after[name], TOL) <= 1.0, name  # element-wise above 1e-3 of the scale
     # the ratio is recomputed from post-solve positions on export / higher-order steps (<= TOL); otherwise it
     # is carried over untouched (bitwise)
     if bool(z["export"]) or S.higher_order_source_on:
@@ -433,4 +435,157 @@ def test_full_size_case_properties():
     dev.run_phase(capi.PH_NEIGHBORS)
     b = dev.run_phase(capi.PH_FLAGS_SOURCE)
     assert (a.n_inner, a.n_surface, a.max_neighbors) == (b.n_inner, b.n_surface, b.max_neighbors)
+    dev.close()
+
+
+@pytest.mark.parametrize("path", U.large_golden_files(), ids=lambda p: p.split("/")[-1][:-4])
+@pytest.mark.parametrize("columns", ["col16", "col32", "matrix_free"])
+def test_large_generated_case_against_reference(path, columns, monkeypatch):
+    """BASELINE configs[3] at nx = 400 ... 2832 (84 k ... 4.04 M particles) against the UNMODIFIED compiled
+    reference, whose digests / counts / strided samples tests/golden/make_large_golden.py recorded on the CPU
+    (one reference step at nx = 2832 is the best part of an hour). Bit-exact: neighbour CSR (order and
+    distances), flags, the assembled PPE (row_start, col, val, rhs). Solve: Eigen's iteration count within 2 %,
+    the raw solution at the sampled rows within 1e-10 of the field's scale and element-wise (tests/util.py
+    elementwise_excess), both on the 16-bit and the int32 column stream. Then the rest of the step from the
+    GPU's own pressure: sampled pressure / minimum pressure / velocity / position within 1e-10."""
+    z = np.load(path)
+    nx = int(z["nx"])
+    if columns == "col32":
+        if nx > 1416:
+            pytest.skip("the int32 column stream is pinned up to nx = 1416; 2832 runs the shipped 16-bit stream")
+        monkeypatch.setenv("MPSB_FORCE_WIDE_COLUMNS", "1")
+    # sweep A of the solve: stored entries (col16 / col32) or recomputed from positions (matrix_free)
+    monkeypatch.setenv("MPSB_MATRIX_FREE", "1" if columns == "matrix_free" else "0")
+    S, t, p, v = U.large_case(z)
+    dev = capi.DeviceMPS(S, t, p, v)
+    dev.load_initial_state()
+    for name, dph, _ in PHASE_MAP[:5]:
+        dev.run_phase(dph)
+    if columns == "col16":  # the digests do not depend on the column stream: once per fixture
+        start, ids, dist = dev.neighbors()
+        assert len(ids) == int(z["nbr_total"]) and int(np.diff(start).max()) == int(z["nbr_max"])
+        assert U.sha(start, ids, dist) == str(z["nbr_digest"]), "neighbour CSR differs from the reference"
+        del start, ids, dist
+    st = dev.run_phase(capi.PH_FLAGS_SOURCE)
+    bc = dev.download(["boundary_condition"])["boundary_condition"]
+    assert U.sha(bc.astype(np.int32)) == str(z["bc_digest"])
+    assert (st.n_inner, st.n_surface) == (int(z["n_inner"]), int(z["n_surface"]))
+    dev.run_phase(capi.PH_MATRIX)
+    st = dev.run_phase(capi.PH_DIRICHLET)
+    assert st.nnz == int(z["nnz"])
+    if columns == "col16":
+        ppe = dev.ppe()
+        assert U.sha(*ppe) == str(z["ppe_digest"]), "assembled PPE differs from the reference"
+        del ppe
+    st = dev.run_phase(capi.PH_SOLVE)
+    ids = z["sample_ids"]
+    x = dev.download(["pressure"])["pressure"]
+    it_ref = int(z["cg_iterations"])
+    err = np.abs(x[ids] - z["sample_solve"]).max() / float(z["p_norminf"])
+    exc = U.elementwise_excess(x[ids], z["sample_solve"], TOL)
+    print(f"{path.split('/')[-1]} {columns}: iterations {st.cg_iterations} vs reference {it_ref}; solve sample "
+          f"max-norm rel {err:.2e}, element-wise excess {exc:.2e}; |p|2 rel "
+          f"{abs(np.sqrt(np.sum(x * x)) - float(z['p_norm2'])) / float(z['p_norm2']):.2e}")
+    assert st.ppe_columns_16bit == (0 if columns == "col32" else 1) and st.solve_in_cluster == 0
+    assert st.ppe_matrix_free == (1 if columns == "matrix_free" else 0)
+    # Iteration count. Eigen sums its dot products serially; that rounding alone delays the crossing of the eps
+    # threshold against the SAME recurrence with tree sums: 999 vs 936 at nx = 400 under every ordering of the
+    # unknowns (profiles/r2_cg_iteration_sensitivity_nx400.txt). The GPU sums in trees, so (a) it may need up to
+    # 12 % fewer iterations than Eigen, never noticeably more, and (b) it must agree within 1 % with the
+    # reference's PPE solved on the CPU by the identical recurrence with pairwise sums (second pin,
+    # tests/golden/make_pairwise_iterations.py).
+    assert 0.88 * it_ref <= st.cg_iterations <= 1.02 * it_ref + 2
+    import json
+    import os
+
+    pw = json.load(open(os.path.join(U.GOLDEN, "large_pairwise_iterations.json")))
+    tag = path.split("large_nx")[-1][:-4]
+    if tag in pw:
+        it_pw = pw[tag]["cg_iterations_pairwise"]
+        print(f"   pairwise-sum CPU recurrence: {it_pw} iterations")
+        assert abs(st.cg_iterations - it_pw) <= max(2, 0.01 * it_pw)
+    assert st.cg_rel_residual <= 2.3e-16
+    assert err <= TOL and exc <= 1.0
+    assert abs(np.sqrt(np.sum(x * x)) - float(z["p_norm2"])) <= TOL * float(z["p_norm2"])
+    assert abs(np.abs(x).max() - float(z["p_norminf"])) <= TOL * float(z["p_norminf"])
+    dev.run_phase(capi.PH_PRESSURE_POST)
+    dev.run_phase(capi.PH_GRADIENT_MOVE)
+    dev.run_phase(capi.PH_NUMBER_DENSITY)
+    courant = dev.run_phase(capi.PH_COURANT).courant
+    got = dev.download()
+    assert U.sha(got["type"]) == str(z["after_type_digest"])
+    assert U.sha(got["boundary_condition"]) == str(z["after_bc_digest"])
+    for name in ("pressure", "minimum_pressure", "velocity", "position", "acceleration", "number_density_ratio"):
+        assert U.rel_err(got[name][ids], z["sample_" + name]) <= TOL, name
+        assert U.elementwise_excess(got[name][ids], z["sample_" + name], TOL) <= 1.0, name
+    assert abs(courant - float(z["courant"])) <= TOL * max(1.0, float(z["courant"]))
+    dev.close()
+
+
+@pytest.mark.parametrize("jitter", [False, True], ids=["lattice", "jittered"])
+def test_matrix_free_operator_matches_the_assembled_matrix(jitter):
+    """The matrix-free sweep A (k_pcg.cu spmv_sweep_mf) recomputes every off-diagonal from the two positions instead of
+    streaming the assembled value. Entry by entry (unit vectors through mpsb_debug_spmv): the stored stream returns
+    the assembled CSR column bit for bit, the recomputation agrees with it to 1e-13 relative (contract: 1e-10,
+    north_star "PPE matrix entries within 1e-10 relative"); on random vectors the two products agree to 1e-13 of
+    the result's scale; the recomputed operator is symmetric to the last bit."""
+    S, t, p, v = C.scaled_dambreak(200)
+    if jitter:
+        p, v = C.jittered(S, t, p, seed=200)
+    dev = capi.DeviceMPS(S, t, p, v)
+    dev.load_initial_state()
+    for name, dph, _ in PHASE_MAP[:8]:
+        dev.run_phase(dph)
+    start, col, val, rhs = dev.ppe()
+    n = len(t)
+    import scipy.sparse as sp
+
+    A = sp.csr_matrix((val, col, start), shape=(n, n))
+    inner = np.flatnonzero(np.diff(start) > 0)
+    rng = np.random.default_rng(5)
+    worst = 0.0
+    cols = {}
+    for j in rng.choice(inner, 24, replace=False):
+        e = np.zeros(n)
+        e[j] = 1.0
+        want = np.asarray(A[:, [j]].todense()).ravel()
+        got_stored, got_mf = dev.spmv(e, 0), dev.spmv(e, 1)
+        assert np.array_equal(got_stored, want), "stored sweep A is not the assembled matrix"
+        nz = want != 0.0
+        assert np.array_equal(got_mf != 0.0, nz), "matrix-free sweep touches a different set of rows"
+        worst = max(worst, float(np.max(np.abs(got_mf[nz] - want[nz]) / np.abs(want[nz]))))
+        cols[int(j)] = got_mf
+    assert worst <= 1e-13, worst
+    # symmetry of the recomputed operator, bit for bit, wherever two sampled columns meet
+    for a in cols:
+        for b in cols:
+            assert cols[a][b] == cols[b][a]
+    x = rng.standard_normal(n)
+    y0, y1 = dev.spmv(x, 0), dev.spmv(x, 1)
+    assert np.abs(y0 - (A @ np.where(np.diff(start) > 0, x, 0.0))).max() <= 1e-13 * np.abs(y0).max()
+    assert np.abs(y1 - y0).max() <= 1e-13 * np.abs(y0).max()
+    print(f"matrix-free entries: worst relative difference {worst:.2e}")
+    dev.close()
+
+
+@pytest.mark.parametrize("path", [p for p in U.golden_files() if "tank3d" not in p], ids=lambda p: p.split("/")[-1][:-4])
+def test_matrix_free_grid_solve_on_the_goldens(path, monkeypatch):
+    """One whole step from the reference's state with the grid kernel forced (no cluster solve, no graph) and sweep A
+    matrix-free, against the reference's own next state: pressure / velocity / position within 1e-10, iteration count
+    within 2 % (the golden sizes are small enough for Eigen's serial sums not to matter)."""
+    monkeypatch.setenv("MPSB_NO_CLUSTER_SOLVE", "1")
+    monkeypatch.setenv("MPSB_NO_STEP_GRAPH", "1")
+    monkeypatch.setenv("MPSB_MATRIX_FREE", "1")
+    z, before, after = U.load_golden(path)
+    S = C.load_case(U.golden_case(path))[0]
+    dev = capi.DeviceMPS(S, before["type"], before["position"], before["velocity"])
+    dev.upload(before)
+    dev.step_forward(bool(z["export"]))
+    got, st = dev.download(), dev.last_stats
+    assert st.ppe_matrix_free == 1 and st.solve_in_cluster == 0
+    assert abs(st.cg_iterations - int(z["cg_iterations"])) <= max(2, 0.02 * int(z["cg_iterations"]))
+    assert np.array_equal(got["boundary_condition"], after["boundary_condition"])
+    for name in ("position", "velocity", "pressure", "minimum_pressure"):
+        assert U.rel_err(got[name], after[name]) <= TOL, name
+        assert U.elementwise_excess(got[name], after[name], TOL) <= 1.0, name
     dev.close()

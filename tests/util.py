@@ -63,3 +63,40 @@ def sealed_box(nx=14, ny=14, l0=0.01):
     pos[:, 0] = ((ix + 0.5) * l0).ravel()
     pos[:, 1] = ((iy + 0.5) * l0).ravel()
     return t, pos, np.zeros_like(pos)
+
+
+def elementwise_excess(a, b, tol, floor_frac=1e-3):
+    """max over entries of |a-b| / (tol * max(|b_i|, floor_frac * max|b|)) — <= 1 means every entry agrees to
+    `tol` RELATIVE TO ITSELF, except entries below floor_frac of the field's largest magnitude, which are held
+    to the absolute bound tol * floor_frac * max|b| (a Krylov solve has a normwise, not a componentwise, error
+    bound, so entries near zero cannot be asked for 1e-10 of themselves)."""
+    a = np.asarray(a, dtype=np.float64)
+    b = np.asarray(b, dtype=np.float64)
+    if b.size == 0:
+        return 0.0
+    scale = float(np.max(np.abs(b)))
+    if scale == 0.0:
+        return 0.0 if not np.any(a) else np.inf
+    return float(np.max(np.abs(a - b) / (tol * np.maximum(np.abs(b), floor_frac * scale))))
+
+
+def large_golden_files():
+    return sorted(glob.glob(os.path.join(GOLDEN, "large_nx*.npz")),
+                  key=lambda p: (int("".join(ch for ch in os.path.basename(p) if ch.isdigit())), p))
+
+
+def sha(*arrays):
+    import hashlib
+
+    h = hashlib.sha256()
+    for a in arrays:
+        h.update(np.ascontiguousarray(a).tobytes())
+    return h.hexdigest()
+
+
+def large_case(z):
+    """Regenerates the inputs of a tests/golden/large_nx*.npz fixture (tests/golden/make_large_golden.py)."""
+    S, t, p, v = C.scaled_dambreak(int(z["nx"]))
+    if int(z["jitter"]):
+        p, v = C.jittered(S, t, p, seed=int(z["nx"]))
+    return S, t, p, v
