@@ -219,9 +219,10 @@ def cpu_points(sizes, budget_s):
     return kind, pts
 
 
-CPU_MODEL_TEXT = ("reference step ~ 2 solves x iterations x (c1 nnz) + c2 n with iterations ~ nx^0.7-0.95 (999 / 1 912 / "
-                  "2 880 at nx = 400 / 800 / 1 416, profiles/r2_cpu_reference_scaling.json), so particle-steps/s "
-                  "FALLS with size; no extrapolated figure is reported as a measurement")
+CPU_MODEL_TEXT = ("measured, not modelled: the reference's step is 2 serial Eigen solves (96-99 % of it); CG iterations "
+                  "999 / 1 912 / 2 880 / 4 221 and 12.9 k / 6.0 k / 2.6 k / 1.7 k particle-steps/s at nx = 400 / 800 / 1 416 / "
+                  "2 832 (profiles/r2_cpu_reference_scaling.json) - CPU throughput FALLS with size, so a ratio against a "
+                  "reduced-size CPU sample understates the same-size ratio; round 1's value*nx_cpu/nx guess is retired")
 
 
 def run_reference_arm(args):

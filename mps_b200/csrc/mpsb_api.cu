@@ -200,6 +200,8 @@ int mpsb_create(const mpsb_settings* settings, int64_t n, const int32_t* type, c
     P.n_active = &P.stats->n_active;
     h->block_hist_cap = 256 * (int) ((N + 2047) / 2048 + 1);
     CKC(dalloc(&h->block_hist, (size_t) h->block_hist_cap));
+    h->scan_status_cap = h->block_hist_cap / 4096 + 2;
+    CKC(dalloc(&h->scan_status, (size_t) h->scan_status_cap + 1)); // [cap] = the ticket counter
     if (mpsb_pcg_configure(h) != 0) {
         snprintf(g_create_error, sizeof g_create_error, "mpsb_create: PCG kernel cannot be made resident");
         mpsb_destroy(h);
@@ -248,7 +250,7 @@ int mpsb_destroy(mpsb_handle* h) {
                     P.val, P.val_alt, P.cell_start, P.cell_end, P.nbr_count, P.nbr_idx, P.nbr_dist, P.ell_count,
                     P.ell_width, P.ell_cmin, P.ell_cmax, P.ell_col, P.ell_col16, P.ell_wide, P.ell_val, P.diag, P.rhs, P.cg_r, P.cg_p, P.cg_ap, P.cg_invdiag, P.cg_partials, P.cg_slice_pap, P.cluster_done, P.row_xy,
                     P.parent, P.mark, P.cand, P.cand_count, P.ev_ghost_id, P.ev_ghost_xyz, P.ev_uncon_id, P.stats,
-                    h->block_hist};
+                    h->block_hist, h->scan_status};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     for (auto& ev : h->ev)

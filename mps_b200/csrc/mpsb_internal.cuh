@@ -172,6 +172,7 @@ struct mpsb_handle {
     int sticky;
     // scratch for the radix sort
     int* block_hist; int block_hist_cap;
+    unsigned long long* scan_status; int scan_status_cap; // look-back scan: one status word per scan tile, then the ticket counter
     void* comm; int rank, world; // multi-GPU (mpsb_comm.cu): MpsbComm*, mirrors P.L.rank / P.L.world
     // host staging for inspection calls
 };
