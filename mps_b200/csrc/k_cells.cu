@@ -275,6 +275,156 @@ __global__ void scatter_all_kernel(Params P) {
     if (s < P.N) scatter_row(P, s);
 }
 
+
+// ---- slab decomposition (world > 1): the build with halo particles and migration folded in -------------------
+// Ownership is by ROW: rank g owns rows [g, g+1) * Np / W of the SORTED order for good; a particle changes owner
+// when the sort gives it a row in another block (migration), and is a halo particle of every rank whose extent
+// (RankExtents) holds its row. Sequence (mpsb_launch_cell_build):
+//   key_rows_kernel      own rows of the OLD order: cell key from the SORTED position      (1/W of the particles)
+//   NCCL all-gather      4 B per particle: the only replicated input
+//   key_by_id_kernel     keys into id order, so that the stable sort leaves ids ascending inside a cell   (replicated)
+//   radix passes         (key, id) pairs                                                             (replicated)
+//   cell_range_kernel    cell ranges, active count, the NEW inverse permutation                     (replicated)
+//   ext_kernel           every rank's extent in the new order, from the sorted keys (binary searches)
+//   scatter_push_kernel  own rows of the OLD order: the particle's state goes into the HOME arrays of every rank
+//                        whose new extent holds its new row — local stores for the bulk, NVLink peer stores for the
+//                        particles that migrate or sit in a neighbour's halo
+//   cross-rank barrier   (k_halo.cu)
+//   gather_ext_kernel    rows of the new extent: HOME -> SORTED, all from local memory
+__device__ __forceinline__ unsigned cell_key_of_position(const Params& P, int type, double x, double y, double z) {
+    if (type == MPSB_GHOST) return MPSB_GHOST_KEY;
+    const double len = P.s.re_max;
+    int ix = (int) ((x - P.s.domain_min[0]) / len) + 1;
+    int iy = (int) ((y - P.s.domain_min[1]) / len) + 1;
+    int iz = (int) ((z - P.s.domain_min[2]) / len) + 1;
+    const bool bad = ix < 1 || ix > P.numX - 2 || iy < 1 || iy > P.numY - 2 || iz < 1 || iz > P.numZ - 2;
+    if (bad) {
+        atomicOr(&P.stats->error_flags, 2);
+        ix = min(max(ix, 0), P.numX - 1);
+        iy = min(max(iy, 0), P.numY - 1);
+        iz = min(max(iz, 0), P.numZ - 1);
+    }
+    return (unsigned) (ix + iy * P.numX + iz * P.numX * P.numY);
+}
+
+__global__ void key_rows_kernel(Params P) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    for (int c = i; c < P.numCells; c += gridDim.x * blockDim.x) {
+        P.cell_start[c] = 0;
+        P.cell_end[c]   = 0;
+    }
+    if (i == 0) *P.n_active = 0;
+    const int s = P.row_lo + i;
+    if (s >= P.row_hi) return;
+    P.keyrow[s] = s < P.N ? cell_key_of_position(P, P.S.type[s], P.S.x[s], P.S.y[s], P.S.z[s]) : MPSB_GHOST_KEY;
+}
+
+__global__ void key_by_id_kernel(Params P) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= P.N) return;
+    const int id = P.S.id[s];
+    P.key[id] = P.keyrow[s];
+    P.val[id] = id;
+}
+
+__global__ void cell_range_kernel(Params P) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= P.N) return;
+    const unsigned k = P.key[s];
+    if (k != MPSB_GHOST_KEY) {
+        if (s == 0 || P.key[s - 1] != k) P.cell_start[k] = s;
+        const unsigned next = (s == P.N - 1) ? MPSB_GHOST_KEY : P.key[s + 1];
+        if (next != k) P.cell_end[k] = s + 1;
+        if (next == MPSB_GHOST_KEY) *P.n_active = s + 1;
+    }
+    P.H.inv_alt[P.val[s]] = s;
+}
+
+// Thread q: rank q's extent in the new order. Neighbour cells of cell c have keys within c +- D, D = 1 + numX
+// (+ numX numY when the domain has thickness in z), so the halo of a block whose active rows carry keys
+// [kmin, kmax] is every active row with a key in [kmin - D, kmax + D].
+__global__ void ext_kernel(Params P) {
+    const int q = threadIdx.x, W = P.L.world;
+    if (q >= W) return;
+    RankExtents& E = *P.ext;
+    const int per = P.Np / W, n = *P.n_active;
+    const int lo = q * per, hi = lo + per;
+    E.own_lo[q] = lo;
+    E.own_hi[q] = hi;
+    if (lo >= n) { // no active row in the block: nothing to search neighbours for
+        E.ext_lo[q] = lo;
+        E.ext_hi[q] = lo;
+        return;
+    }
+    const int last = min(hi, n) - 1;
+    const unsigned flat = P.s.domain_max[2] == P.s.domain_min[2] ? 0u : 1u;
+    const unsigned D = 1u + (unsigned) P.numX + flat * (unsigned) (P.numX * P.numY);
+    const unsigned kmin = P.key[lo], kmax = P.key[last];
+    const unsigned klo = kmin > D ? kmin - D : 0u, khi = kmax + D;
+    int a = 0, b = n; // first row with key >= klo
+    while (a < b) {
+        const int m = (a + b) >> 1;
+        if (P.key[m] < klo) a = m + 1; else b = m;
+    }
+    E.ext_lo[q] = min(a, lo);
+    a = 0; b = n; // first row with key > khi
+    while (a < b) {
+        const int m = (a + b) >> 1;
+        if (P.key[m] <= khi) a = m + 1; else b = m;
+    }
+    E.ext_hi[q] = max(a, last + 1);
+}
+
+__device__ __forceinline__ bool rank_holds_row(const RankExtents& E, int q, int row) {
+    return (row >= E.own_lo[q] && row < E.own_hi[q]) || (row >= E.ext_lo[q] && row < E.ext_hi[q]);
+}
+
+__global__ void __launch_bounds__(256) scatter_push_kernel(Params P) {
+    const int s = P.row_lo + blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= P.row_hi || s >= P.N) return;
+    const int id = P.S.id[s], nr = P.H.inv_alt[id];
+    const RankExtents& E = *P.ext;
+    const double x = P.S.x[s], y = P.S.y[s], z = P.S.z[s], u = P.S.u[s], v = P.S.v[s], w = P.S.w[s];
+    const double ax = P.S.ax[s], ay = P.S.ay[s], az = P.S.az[s], pr = P.S.p[s], mp = P.S.minp[s], ra = P.S.ratio[s];
+    const int ty = P.S.type[s], bc = P.S.bc[s];
+    const Home& H = P.H;
+    for (int q = 0; q < P.L.world; q++) {
+        if (!rank_holds_row(E, q, nr)) continue;
+        double *pos = H.pos, *vel = H.vel, *acc = H.acc, *hp = H.p, *hm = H.minp, *hr = H.ratio;
+        int *ht = H.type, *hb = H.bc;
+        if (q != P.L.rank) {
+            pos = mpsb_peer(P, pos, q); vel = mpsb_peer(P, vel, q); acc = mpsb_peer(P, acc, q);
+            hp = mpsb_peer(P, hp, q); hm = mpsb_peer(P, hm, q); hr = mpsb_peer(P, hr, q);
+            ht = mpsb_peer(P, ht, q); hb = mpsb_peer(P, hb, q);
+        }
+        pos[3 * id] = x; pos[3 * id + 1] = y; pos[3 * id + 2] = z;
+        vel[3 * id] = u; vel[3 * id + 1] = v; vel[3 * id + 2] = w;
+        acc[3 * id] = ax; acc[3 * id + 1] = ay; acc[3 * id + 2] = az;
+        hp[id] = pr; hm[id] = mp; hr[id] = ra;
+        ht[id] = ty; hb[id] = bc;
+    }
+}
+
+__global__ void __launch_bounds__(256) gather_ext_kernel(Params P) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= P.N) return;
+    const int id = P.val[s];
+    P.S.id[s] = id; // the permutation is replicated: every row, whoever owns it
+    if (!rank_holds_row(*P.ext, P.L.rank, s)) return;
+    const Home& H = P.H;
+    P.S.x[s] = H.pos[3 * id]; P.S.y[s] = H.pos[3 * id + 1]; P.S.z[s] = H.pos[3 * id + 2];
+    P.S.u[s] = H.vel[3 * id]; P.S.v[s] = H.vel[3 * id + 1]; P.S.w[s] = H.vel[3 * id + 2];
+    P.S.ax[s] = H.acc[3 * id]; P.S.ay[s] = H.acc[3 * id + 1]; P.S.az[s] = H.acc[3 * id + 2];
+    P.S.minp[s] = H.minp[id]; P.S.ratio[s] = H.ratio[id];
+    P.S.type[s] = H.type[id];
+    // The halo copies of the flags and the pressure have ONE writer: the owner's halo push (k_halo.cu), which may
+    // already be under way on a faster peer while this kernel still runs. Only own rows take them from HOME.
+    if (s >= P.row_lo && s < P.row_hi) {
+        P.S.p[s]  = H.p[id];
+        P.S.bc[s] = H.bc[id];
+    }
+}
+
 // ---- small systems: the whole build in ONE launch ----------------------------------------------------
 // The shipped cases (458 - 6 146 particles) are bound by the length of the launch chain, and the build above
 // is 10 launches, three times per step. Up to small_build_max_n particles one CTA does all of it, phases
@@ -385,7 +535,18 @@ void mpsb_launch_gather_all(mpsb_handle* h) {
     MPSB_LAUNCH(h, gather_all_kernel, mpsb_div_up(P.N, 256), 256, 0, P, 0);
 }
 
+// End of a step / phase: one GPU writes every row back to HOME; with several ranks HOME is brought up to date
+// lazily and collectively (mpsb_comm_sync_home) only when the host asks for the state.
 void mpsb_launch_scatter_all(mpsb_handle* h) {
+    Params& P = h->P;
+    if (h->world > 1) {
+        h->home_current = false;
+        return;
+    }
+    MPSB_LAUNCH(h, scatter_all_kernel, mpsb_div_up(P.N, 256), 256, 0, P);
+}
+
+void mpsb_launch_scatter_all_rows(mpsb_handle* h) {
     Params& P = h->P;
     MPSB_LAUNCH(h, scatter_all_kernel, mpsb_div_up(P.N, 256), 256, 0, P);
 }
@@ -394,6 +555,30 @@ void mpsb_launch_scatter_all(mpsb_handle* h) {
 void mpsb_launch_cell_build(mpsb_handle* h, bool scatter_first) {
     Params& P   = h->P;
     int N       = P.N;
+    if (h->world > 1) {
+        const int grid = mpsb_div_up(N, 256), tiles = mpsb_div_up(N, SORT_TILE);
+        const int scan_tiles = mpsb_div_up(RADIX * tiles, SCAN_TILE);
+        MPSB_LAUNCH(h, key_rows_kernel, mpsb_div_up(P.Np / h->world, 256), 256, 0, P);
+        if (mpsb_comm_allgather_keyrow(h)) return;
+        MPSB_LAUNCH(h, key_by_id_kernel, grid, 256, 0, P);
+        for (int shift = 0; shift < h->sort_bits; shift += 8) {
+            MPSB_LAUNCH(h, radix_hist_kernel, tiles, SORT_THREADS, 0, P.key, N, shift, tiles, h->block_hist);
+            MPSB_LAUNCH(h, scan_lookback_kernel, scan_tiles, SCAN_THREADS, 0, h->block_hist, RADIX * tiles, scan_tiles,
+                        h->scan_status, h->scan_status + h->scan_status_cap);
+            MPSB_LAUNCH(h, radix_scatter_kernel, tiles, SORT_THREADS, 0, P.key, P.val, P.key_alt, P.val_alt, N, shift,
+                        tiles, h->block_hist);
+            unsigned* tk = P.key; P.key = P.key_alt; P.key_alt = tk;
+            int* tv = P.val; P.val = P.val_alt; P.val_alt = tv;
+        }
+        MPSB_LAUNCH(h, cell_range_kernel, grid, 256, 0, P);
+        MPSB_LAUNCH(h, ext_kernel, 1, 32, 0, P);
+        MPSB_LAUNCH(h, scatter_push_kernel, mpsb_own_grid(h, 256), 256, 0, P);
+        mpsb_launch_xbarrier(h);
+        MPSB_LAUNCH(h, gather_ext_kernel, grid, 256, 0, P);
+        int* ti = P.H.inv; P.H.inv = P.H.inv_alt; P.H.inv_alt = ti;
+        h->home_current = false;
+        return;
+    }
     if (N <= h->small_build_max_n && P.numCells <= 8 * h->small_build_max_n && P.numCells <= SMALL_BUILD_MAX_CELLS) {
         MPSB_LAUNCH(h, small_cell_build_kernel, 1, SMALL_BUILD_THREADS, 0, P, scatter_first ? 1 : 0);
         return;

@@ -33,7 +33,8 @@ __device__ __forceinline__ void ghost_event(const Params& P, int s, double x, do
 
 // Reads neighbours' OLD velocity (u,v,w), writes the new one to (u2,v2,w2); the host swaps.
 __global__ void __launch_bounds__(256) explicit_kernel(Params P) {
-    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    int s = P.row_lo + blockIdx.x * blockDim.x + threadIdx.x; // own rows (one GPU: all of them)
+    if (s >= P.row_hi) return;
     if (s >= P.N) return;
     double u = P.S.u[s], v = P.S.v[s], w = P.S.w[s];
     if (s < *P.n_active && P.S.type[s] == MPSB_FLUID) {
@@ -74,7 +75,8 @@ __global__ void __launch_bounds__(256) explicit_kernel(Params P) {
 // velocities. Candidate membership depends only on the stale list distances and on types, neither
 // of which changes during the loop, so the candidate set equals the reference's.
 __global__ void __launch_bounds__(256) collision_candidates_kernel(Params P) {
-    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    int s = P.row_lo + blockIdx.x * blockDim.x + threadIdx.x; // own rows (one GPU: all of them)
+    if (s >= P.row_hi) return;
     if (s >= *P.n_active || P.S.type[s] != MPSB_FLUID) return;
     int cnt = P.nbr_count[s], id = P.S.id[s];
     // candidates are rare: only the distances are batched, the neighbour's type and id are read on a hit
@@ -151,9 +153,156 @@ __global__ void __launch_bounds__(1024) collision_replay_kernel(Params P) {
     }
 }
 
+
+// ---- collision across ranks (slab decomposition) -------------------------------------------------------------
+// The reference loop is ONE serial sweep over all particles (src/mps.cpp:217-250): a pair in one slab can feed a
+// chain that ends in another. So the candidates are found per rank (own rows), but every rank replays ALL of them,
+// identically: each owner stores its candidates as self-contained records — visiting-order key plus the
+// pre-collision position / velocity of both particles (halo copies are current: the lists were just built) — into
+// its segment of EVERY rank's record inbox over NVLink, a cross-rank barrier publishes them, and one CTA per rank
+// sorts the keys and replays the pairs serially on a compact copy of the particles the records touch (P.mark maps
+// row -> compact slot), exactly the arithmetic of collision_replay_kernel. Own rows then take their new state from
+// the compact copy; halo copies are refreshed by the list build that follows.
+__global__ void __launch_bounds__(256) collision_records_kernel(Params P) {
+    int s = P.row_lo + blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= P.row_hi || s >= *P.n_active || P.S.type[s] != MPSB_FLUID) return;
+    int cnt = P.nbr_count[s], id = P.S.id[s];
+    mpsb_walk_list<8, MpsbNoRec>(
+        P, s, cnt, [](int) { return MpsbNoRec{}; },
+        [&](int k, double d, int j, const MpsbNoRec&) {
+            if (d < P.s.collision_distance) {
+                const int tj = P.S.type[j];
+                if (tj == MPSB_FLUID && P.S.id[j] >= id) return;
+                int c = atomicAdd(P.cand_count, 1);
+                if (c >= P.crec_seg) {
+                    atomicOr(&P.stats->error_flags, 1);
+                    return;
+                }
+                CollisionRecord r;
+                r.key    = ((unsigned long long) (unsigned) id << 32) | ((unsigned long long) (unsigned) k << 20);
+                r.row_i  = s;
+                r.row_j  = j;
+                r.type_j = tj;
+                r.pad    = 0;
+                r.dist   = d;
+                r.xi[0] = P.S.x[s]; r.xi[1] = P.S.y[s]; r.xi[2] = P.S.z[s];
+                r.ui[0] = P.S.u[s]; r.ui[1] = P.S.v[s]; r.ui[2] = P.S.w[s];
+                r.xj[0] = P.S.x[j]; r.xj[1] = P.S.y[j]; r.xj[2] = P.S.z[j];
+                r.uj[0] = P.S.u[j]; r.uj[1] = P.S.v[j]; r.uj[2] = P.S.w[j];
+                const size_t at = (size_t) P.L.rank * P.crec_seg + c;
+                for (int q = 0; q < P.L.world; q++) mpsb_peer(P, P.crec, q)[at] = r;
+            }
+        });
+}
+
+__global__ void collision_count_push_kernel(Params P) {
+    if (threadIdx.x != 0) return;
+    const int n = min(*P.cand_count, P.crec_seg);
+    *P.cand_count = 0;
+    for (int q = 0; q < P.L.world; q++) mpsb_peer(P, P.crec_count, q)[P.L.rank] = n;
+}
+
+__global__ void __launch_bounds__(1024) collision_replay_records_kernel(Params P) {
+    __shared__ int offset[MPSB_MAX_RANKS + 1];
+    const int W = P.L.world;
+    if (threadIdx.x == 0) {
+        offset[0] = 0;
+        for (int q = 0; q < W; q++) offset[q + 1] = offset[q] + P.crec_count[q];
+        P.stats->n_collisions = offset[W];
+    }
+    __syncthreads();
+    const int M = offset[W];
+    if (M == 0) return;
+    // keys with the record index in the low 20 bits; forget stale row -> slot entries
+    for (int q = 0; q < W; q++)
+        for (int c = threadIdx.x; c < P.crec_count[q]; c += blockDim.x) {
+            const int at = q * P.crec_seg + c;
+            const CollisionRecord& r = P.crec[at];
+            P.cand[offset[q] + c] = r.key | (unsigned long long) at;
+            P.mark[r.row_i] = 0;
+            P.mark[r.row_j] = 0;
+        }
+    int M2 = 1;
+    while (M2 < M) M2 <<= 1;
+    for (int i = M + threadIdx.x; i < M2; i += blockDim.x) P.cand[i] = ~0ull;
+    __syncthreads();
+    for (int size = 2; size <= M2; size <<= 1)
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            for (int t = threadIdx.x; t < (M2 >> 1); t += blockDim.x) {
+                int lo = 2 * t - (t & (stride - 1)), hi = lo + stride;
+                bool up = (lo & size) == 0;
+                unsigned long long a = P.cand[lo], b = P.cand[hi];
+                if ((a > b) == up) {
+                    P.cand[lo] = b;
+                    P.cand[hi] = a;
+                }
+            }
+            __syncthreads();
+        }
+    const int cap = 2 * W * P.crec_seg;
+    double *cx = P.cstate, *cy = cx + cap, *cz = cy + cap, *cu = cz + cap, *cv = cu + cap, *cw = cv + cap;
+    if (threadIdx.x == 0) {
+        const double col = P.s.collision_distance, e = P.s.restitution;
+        int used = 0;
+        auto slot_of = [&](int row, const double* x, const double* u) -> int {
+            int m = P.mark[row];
+            if (m == 0) {
+                m = ++used;
+                P.mark[row] = m;
+                cx[m - 1] = x[0]; cy[m - 1] = x[1]; cz[m - 1] = x[2];
+                cu[m - 1] = u[0]; cv[m - 1] = u[1]; cw[m - 1] = u[2];
+            }
+            return m - 1;
+        };
+        for (int c = 0; c < M; c++) {
+            const CollisionRecord& r = P.crec[(int) (P.cand[c] & 0xFFFFFull)];
+            const int a = slot_of(r.row_i, r.xi, r.ui), b = slot_of(r.row_j, r.xj, r.uj);
+            const double dist = r.dist;
+            double invMi = P.inv_density;
+            double invMj = r.type_j == MPSB_FLUID ? P.inv_density : 0.0;
+            double reducedMass = 1.0 / (invMi + invMj);
+            double dx = cx[b] - cx[a], dy = cy[b] - cy[a], dz = cz[b] - cz[a];
+            double z2 = (dx * dx + dy * dy) + dz * dz;
+            double nx = dx, ny = dy, nz = dz;
+            if (z2 > 0.0) {
+                double sz = sqrt(z2);
+                nx = dx / sz; ny = dy / sz; nz = dz / sz;
+            }
+            double du = cu[b] - cu[a], dv = cv[b] - cv[a], dw = cw[b] - cw[a];
+            double rel = (du * nx + dv * ny) + dw * nz;
+            if (rel < 0.0) {
+                double impulse = -(1.0 + e) * rel * reducedMass;
+                double ci = impulse * invMi, cj = impulse * invMj;
+                cu[a] -= ci * nx; cv[a] -= ci * ny; cw[a] -= ci * nz;
+                cu[b] += cj * nx; cv[b] += cj * ny; cw[b] += cj * nz;
+                double depth = col - dist;
+                double posImpulse = depth * reducedMass;
+                double pi = posImpulse * invMi, pj = posImpulse * invMj;
+                cx[a] -= pi * nx; cy[a] -= pi * ny; cz[a] -= pi * nz;
+                cx[b] += pj * nx; cy[b] += pj * ny; cz[b] += pj * nz;
+            }
+        }
+    }
+    __syncthreads();
+    // own rows take their state from the compact copy (several records may name the same row: same value)
+    for (int q = 0; q < W; q++)
+        for (int c = threadIdx.x; c < P.crec_count[q]; c += blockDim.x) {
+            const CollisionRecord& r = P.crec[q * P.crec_seg + c];
+            const int rows[2] = {r.row_i, r.row_j};
+            for (int t = 0; t < 2; t++) {
+                const int row = rows[t];
+                if (row < P.row_lo || row >= P.row_hi) continue;
+                const int m = P.mark[row] - 1;
+                P.S.x[row] = cx[m]; P.S.y[row] = cy[m]; P.S.z[row] = cz[m];
+                P.S.u[row] = cu[m]; P.S.v[row] = cv[m]; P.S.w[row] = cw[m];
+            }
+        }
+}
+
 // ---- pressure gradient and correction ----------------------------------------------------------------
 __global__ void __launch_bounds__(256) gradient_kernel(Params P) {
-    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    int s = P.row_lo + blockIdx.x * blockDim.x + threadIdx.x; // own rows (one GPU: all of them)
+    if (s >= P.row_hi) return;
     if (s >= *P.n_active || P.S.type[s] != MPSB_FLUID) return;
     const double re = P.s.re_pressure;
     const double xi = P.S.x[s], yi = P.S.y[s], zi = P.S.z[s], pmin = P.S.minp[s];
@@ -178,7 +327,8 @@ __global__ void __launch_bounds__(256) gradient_kernel(Params P) {
 }
 
 __global__ void __launch_bounds__(256) move2_kernel(Params P) {
-    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    int s = P.row_lo + blockIdx.x * blockDim.x + threadIdx.x; // own rows (one GPU: all of them)
+    if (s >= P.row_hi) return;
     if (s >= *P.n_active || P.S.type[s] != MPSB_FLUID) return;
     const double dt = P.s.dt;
     double ax = P.S.ax[s], ay = P.S.ay[s], az = P.S.az[s];
@@ -193,7 +343,8 @@ __global__ void __launch_bounds__(256) move2_kernel(Params P) {
 }
 
 __global__ void __launch_bounds__(256) courant_kernel(Params P) {
-    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    int s = P.row_lo + blockIdx.x * blockDim.x + threadIdx.x; // own rows (one GPU: all of them)
+    if (s >= P.row_hi) return;
     double c = 0.0;
     if (s < *P.n_active && P.S.type[s] == MPSB_FLUID) {
         double u = P.S.u[s], v = P.S.v[s], w = P.S.w[s];
@@ -211,7 +362,7 @@ __global__ void __launch_bounds__(256) courant_kernel(Params P) {
 
 void mpsb_launch_explicit(mpsb_handle* h) {
     Params& P = h->P;
-    MPSB_LAUNCH(h, explicit_kernel, mpsb_div_up(P.N, 256), 256, 0, P);
+    MPSB_LAUNCH(h, explicit_kernel, mpsb_own_grid(h, 256), 256, 0, P);
     double* t;
     t = P.S.u; P.S.u = P.S.u2; P.S.u2 = t;
     t = P.S.v; P.S.v = P.S.v2; P.S.v2 = t;
@@ -220,18 +371,25 @@ void mpsb_launch_explicit(mpsb_handle* h) {
 
 void mpsb_launch_collision(mpsb_handle* h) {
     Params& P = h->P;
-    MPSB_LAUNCH(h, collision_candidates_kernel, mpsb_div_up(P.N, 256), 256, 0, P);
+    if (h->world > 1) {
+        MPSB_LAUNCH(h, collision_records_kernel, mpsb_own_grid(h, 256), 256, 0, P);
+        MPSB_LAUNCH(h, collision_count_push_kernel, 1, 32, 0, P);
+        mpsb_launch_xbarrier(h);
+        MPSB_LAUNCH(h, collision_replay_records_kernel, 1, 1024, 0, P);
+        return;
+    }
+    MPSB_LAUNCH(h, collision_candidates_kernel, mpsb_own_grid(h, 256), 256, 0, P);
     MPSB_LAUNCH(h, collision_replay_kernel, 1, 1024, 0, P);
 }
 
 void mpsb_launch_gradient_move(mpsb_handle* h) {
     Params& P = h->P;
-    MPSB_LAUNCH(h, gradient_kernel, mpsb_div_up(P.N, 256), 256, 0, P);
-    MPSB_LAUNCH(h, move2_kernel, mpsb_div_up(P.N, 256), 256, 0, P);
+    MPSB_LAUNCH(h, gradient_kernel, mpsb_own_grid(h, 256), 256, 0, P);
+    MPSB_LAUNCH(h, move2_kernel, mpsb_own_grid(h, 256), 256, 0, P);
 }
 
 void mpsb_launch_courant(mpsb_handle* h) {
     Params& P = h->P;
     if (!h->in_step) cudaMemsetAsync(&P.stats->courant_bits_as_double, 0, sizeof(double), h->stream); // a step clears all stats at once
-    MPSB_LAUNCH(h, courant_kernel, mpsb_div_up(P.N, 256), 256, 0, P);
+    MPSB_LAUNCH(h, courant_kernel, mpsb_own_grid(h, 256), 256, 0, P);
 }

@@ -11,7 +11,8 @@
 namespace {
 
 __global__ void __launch_bounds__(128) neighbor_kernel(Params P) {
-    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    int s = P.row_lo + blockIdx.x * blockDim.x + threadIdx.x; // own rows (one GPU: all of them)
+    if (s >= P.row_hi) return;
     int n_active = *P.n_active;
     if (s >= P.N) return;
     if (s >= n_active) {
@@ -96,7 +97,8 @@ __global__ void __launch_bounds__(128) neighbor_kernel(Params P) {
 
 // ratio = Surface ? 0 : n(re_p) / n0_p   (src/mps.cpp:630-640); ghosts keep their last value.
 __global__ void number_density_kernel(Params P) {
-    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    int s = P.row_lo + blockIdx.x * blockDim.x + threadIdx.x; // own rows (one GPU: all of them)
+    if (s >= P.row_hi) return;
     if (s >= *P.n_active) return;
     double ratio = 0.0;
     if (P.S.bc[s] != MPSB_BC_SURFACE) {
@@ -120,10 +122,10 @@ __global__ void number_density_kernel(Params P) {
 
 void mpsb_launch_neighbors(mpsb_handle* h) {
     Params& P = h->P;
-    MPSB_LAUNCH(h, neighbor_kernel, mpsb_div_up(P.N, 128), 128, 0, P);
+    MPSB_LAUNCH(h, neighbor_kernel, mpsb_own_grid(h, 128), 128, 0, P);
 }
 
 void mpsb_launch_number_density(mpsb_handle* h) {
     Params& P = h->P;
-    MPSB_LAUNCH(h, number_density_kernel, mpsb_div_up(P.N, 256), 256, 0, P);
+    MPSB_LAUNCH(h, number_density_kernel, mpsb_own_grid(h, 256), 256, 0, P);
 }

@@ -12,7 +12,8 @@ namespace {
 // Boundary-condition flag for every slot and, for the standard source term, b_i in the same pass
 // over the distances (re_s and re_p sums are kept separate so differing radii stay exact).
 __global__ void __launch_bounds__(256) flags_kernel(Params P) {
-    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    int s = P.row_lo + blockIdx.x * blockDim.x + threadIdx.x; // own rows (one GPU: all of them)
+    if (s >= P.row_hi) return;
     if (s >= P.N) return;
     int bc = MPSB_BC_IGNORED;
     double b = 0.0;
@@ -50,7 +51,8 @@ __global__ void __launch_bounds__(256) flags_kernel(Params P) {
 
 // Higher-order source term (src/mps.cpp:288-307); needs the neighbours' flags, hence a second pass.
 __global__ void __launch_bounds__(256) source_ho_kernel(Params P) {
-    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    int s = P.row_lo + blockIdx.x * blockDim.x + threadIdx.x; // own rows (one GPU: all of them)
+    if (s >= P.row_hi) return;
     if (s >= *P.n_active || P.S.bc[s] != MPSB_BC_INNER) return;
     const double re = P.s.re_pressure;
     const double xi = P.S.x[s], yi = P.S.y[s], zi = P.S.z[s];
@@ -79,8 +81,9 @@ __global__ void __launch_bounds__(256) source_ho_kernel(Params P) {
 // without per-row trip counts; adding +0.0 * p never changes a finite sum. One warp = one slice, so
 // the grid covers Np rows and no thread exits before the warp-wide maximum.
 __global__ void __launch_bounds__(256) matrix_kernel(Params P, int force_wide) {
-    int s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s == 0 && force_wide) *P.ell_wide = 1;
+    int s = P.row_lo + blockIdx.x * blockDim.x + threadIdx.x; // own rows (one GPU: all of them)
+    if (s >= P.row_hi) return;
+    if (s == P.row_lo && force_wide) *P.ell_wide = 1;
     if (s >= P.Np) return; // Np is a multiple of 32: whole warps leave together
     int m = 0, cmin = s, cmax = s, wide = 0;
     double diag = 0.0;
@@ -138,6 +141,13 @@ __global__ void __launch_bounds__(256) matrix_kernel(Params P, int force_wide) {
 // non-ghost particles (DummyWall included) and doubles the diagonal of Inner particles it never
 // reaches. The neighbour relation is symmetric, so "reached" == "in a connected component that
 // holds a Surface particle": lock-free union-find (hook larger root under smaller, CAS) + marking.
+__device__ __forceinline__ bool in_extent(const Params& P, int s) {
+    if (P.L.world <= 1) return true;
+    const RankExtents& E = *P.ext;
+    const int q = P.L.rank;
+    return (s >= E.own_lo[q] && s < E.own_hi[q]) || (s >= E.ext_lo[q] && s < E.ext_hi[q]);
+}
+
 __device__ __forceinline__ int uf_find(int* parent, int x) {
     int p = parent[x];
     while (p != x) {
@@ -150,21 +160,24 @@ __device__ __forceinline__ int uf_find(int* parent, int x) {
 }
 
 __global__ void dirichlet_init_kernel(Params P) {
-    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    int s = blockIdx.x * blockDim.x + threadIdx.x; // rows of this rank's extent: own + halo (one GPU: all rows)
+    if (s < P.N && !in_extent(P, s)) return;
     if (s >= P.N) return;
     P.parent[s] = s;
     P.mark[s]   = 0;
 }
 
 __global__ void __launch_bounds__(256) dirichlet_union_kernel(Params P) {
-    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    int s = P.row_lo + blockIdx.x * blockDim.x + threadIdx.x; // own rows (one GPU: all of them)
+    if (s >= P.row_hi) return;
     if (s >= *P.n_active) return;
     const double re = P.s.re_pressure;
     int cnt = P.nbr_count[s];
     mpsb_walk_list<8, MpsbNoRec>(
         P, s, cnt, [](int) { return MpsbNoRec{}; },
         [&](int, double d, int j, const MpsbNoRec&) {
-            if (j > s || !(d < re)) return; // each undirected edge once
+            // each undirected edge once; an edge to a halo row above this rank's block belongs to nobody else here
+            if (!(d < re) || (j > s && j < P.row_hi)) return;
             int a = uf_find(P.parent, s), b = uf_find(P.parent, j);
             while (a != b) {
                 if (a < b) { int t = a; a = b; b = t; }
@@ -177,13 +190,15 @@ __global__ void __launch_bounds__(256) dirichlet_union_kernel(Params P) {
 }
 
 __global__ void dirichlet_mark_kernel(Params P) {
-    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    int s = blockIdx.x * blockDim.x + threadIdx.x; // rows of this rank's extent: own + halo (one GPU: all rows)
+    if (s < P.N && !in_extent(P, s)) return;
     if (s >= *P.n_active) return;
     if (P.S.bc[s] == MPSB_BC_SURFACE) P.mark[uf_find(P.parent, s)] = 1;
 }
 
 __global__ void dirichlet_apply_kernel(Params P) {
-    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    int s = P.row_lo + blockIdx.x * blockDim.x + threadIdx.x; // own rows (one GPU: all of them)
+    if (s >= P.row_hi) return;
     if (s >= *P.n_active || P.S.bc[s] != MPSB_BC_INNER) return;
     if (!P.mark[uf_find(P.parent, s)]) {
         P.diag[s] *= 2.0; // coefficientMatrix.coeffRef(i, i) *= 2.0 (src/mps.cpp:412)
@@ -192,15 +207,52 @@ __global__ void dirichlet_apply_kernel(Params P) {
     }
 }
 
+// Several ranks (slab decomposition): a rank's union-find covers the edges incident to its OWN rows, with its halo
+// rows as extra nodes, so a component that reaches a Surface particle only through another rank's rows is not
+// marked yet. Marks are propagated to a fixpoint: every owner stores, for each own row that is some peer's halo
+// row, whether the row's local component is marked into that peer's `reach` array; after the cross-rank barrier
+// every rank folds the reach flags of its halo rows into its local components. Each edge of the global graph
+// lies in the local graph of the owner(s) of its end points and neighbouring local graphs share those end points,
+// so the fixpoint is the reference's answer (reached from a Surface particle <=> component holds one). Rounds are
+// driven by the host (one 2-int all-reduce each): typically one per slab between a row and the free surface.
+__global__ void __launch_bounds__(256) dirichlet_reach_push_kernel(Params P) {
+    int s = P.row_lo + blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= P.row_hi || s >= *P.n_active) return;
+    const RankExtents& E = *P.ext;
+    bool boundary = false;
+    for (int q = 0; q < P.L.world; q++) boundary |= q != P.L.rank && s >= E.ext_lo[q] && s < E.ext_hi[q];
+    const bool inner = P.S.bc[s] == MPSB_BC_INNER;
+    if (!boundary && !inner) return;
+    const int v = P.mark[uf_find(P.parent, s)];
+    if (inner && !v) P.dflags[1] = 1; // still unresolved somewhere: another round may be needed
+    if (!boundary) return;
+    for (int q = 0; q < P.L.world; q++)
+        if (q != P.L.rank && s >= E.ext_lo[q] && s < E.ext_hi[q]) mpsb_peer(P, P.reach, q)[s] = v;
+}
+
+__global__ void __launch_bounds__(256) dirichlet_absorb_kernel(Params P) {
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= *P.n_active || (s >= P.row_lo && s < P.row_hi) || !in_extent(P, s)) return;
+    if (P.reach[s]) {
+        const int r = uf_find(P.parent, s);
+        if (!P.mark[r]) {
+            P.mark[r]   = 1;
+            P.dflags[0] = 1;
+        }
+    }
+}
+
 // ---- after the solve -----------------------------------------------------------------------------------
 __global__ void clamp_kernel(Params P) {
-    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    int s = P.row_lo + blockIdx.x * blockDim.x + threadIdx.x; // own rows (one GPU: all of them)
+    if (s >= P.row_hi) return;
     if (s >= P.N) return;
     if (P.S.p[s] < 0.0) P.S.p[s] = 0.0; // NaN passes through, like the reference (:475)
 }
 
 __global__ void __launch_bounds__(256) min_pressure_kernel(Params P) {
-    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    int s = P.row_lo + blockIdx.x * blockDim.x + threadIdx.x; // own rows (one GPU: all of them)
+    if (s >= P.row_hi) return;
     if (s >= *P.n_active || P.S.bc[s] == MPSB_BC_IGNORED) return;
     const double re = P.s.re_pressure;
     double m = P.S.p[s];
@@ -221,9 +273,13 @@ __global__ void __launch_bounds__(256) min_pressure_kernel(Params P) {
 
 void mpsb_launch_flags_source(mpsb_handle* h) {
     Params& P = h->P;
-    int grid  = mpsb_div_up(P.N, 256);
+    int grid  = mpsb_own_grid(h, 256);
     if (!h->in_step) cudaMemsetAsync(&P.stats->n_inner, 0, 2 * sizeof(int), h->stream); // n_inner, n_surface (a step clears all stats at once)
     MPSB_LAUNCH(h, flags_kernel, grid, 256, 0, P);
+    if (h->world > 1) { // the assembly, the higher-order source term and the Dirichlet check read the neighbours' flags
+        mpsb_launch_halo_push_bc(h);
+        mpsb_launch_xbarrier(h);
+    }
     if (P.s.higher_order_source_on) MPSB_LAUNCH(h, source_ho_kernel, grid, 256, 0, P);
 }
 
@@ -232,22 +288,37 @@ void mpsb_launch_matrix(mpsb_handle* h) {
     if (!h->in_step) cudaMemsetAsync(&P.stats->nnz, 0, sizeof(int), h->stream);
     const char* force = getenv("MPSB_FORCE_WIDE_COLUMNS"); // tests: exercise the 32-bit column stream
     // *ell_wide is cleared by the solve that consumed it (pcg_kernel), not by a memset node here
-    MPSB_LAUNCH(h, matrix_kernel, mpsb_div_up(P.Np, 256) , 256, 0, P, force && atoi(force) ? 1 : 0);
+    MPSB_LAUNCH(h, matrix_kernel, mpsb_div_up(P.row_hi - P.row_lo, 256), 256, 0, P, force && atoi(force) ? 1 : 0);
 }
 
 void mpsb_launch_dirichlet(mpsb_handle* h) {
     Params& P = h->P;
-    int grid  = mpsb_div_up(P.N, 256);
+    int grid = mpsb_own_grid(h, 256), grid_all = mpsb_div_up(P.N, 256);
     if (!h->in_step) cudaMemsetAsync(&P.stats->n_unconnected, 0, sizeof(int), h->stream);
-    MPSB_LAUNCH(h, dirichlet_init_kernel, grid, 256, 0, P);
+    MPSB_LAUNCH(h, dirichlet_init_kernel, grid_all, 256, 0, P);
     MPSB_LAUNCH(h, dirichlet_union_kernel, grid, 256, 0, P);
-    MPSB_LAUNCH(h, dirichlet_mark_kernel, grid, 256, 0, P);
+    MPSB_LAUNCH(h, dirichlet_mark_kernel, grid_all, 256, 0, P);
+    if (h->world > 1) {
+        for (int round = 0; round < 4096; round++) {
+            cudaMemsetAsync(P.dflags, 0, 2 * sizeof(int), h->stream);
+            MPSB_LAUNCH(h, dirichlet_reach_push_kernel, grid, 256, 0, P);
+            mpsb_launch_xbarrier(h);
+            MPSB_LAUNCH(h, dirichlet_absorb_kernel, grid_all, 256, 0, P);
+            int flags[2] = {0, 0};
+            if (mpsb_comm_allreduce_dflags(h, flags)) return; // sticky error set
+            if (!flags[0] || !flags[1]) break; // no mark changed anywhere, or every Inner row everywhere is connected
+        }
+    }
     MPSB_LAUNCH(h, dirichlet_apply_kernel, grid, 256, 0, P);
 }
 
 void mpsb_launch_pressure_post(mpsb_handle* h) {
     Params& P = h->P;
-    int grid  = mpsb_div_up(P.N, 256);
+    int grid  = mpsb_own_grid(h, 256);
     MPSB_LAUNCH(h, clamp_kernel, grid, 256, 0, P);
+    if (h->world > 1) { // minimum pressure and the gradient read the neighbours' (clamped) pressures
+        mpsb_launch_halo_push_p(h);
+        mpsb_launch_xbarrier(h);
+    }
     MPSB_LAUNCH(h, min_pressure_kernel, grid, 256, 0, P);
 }

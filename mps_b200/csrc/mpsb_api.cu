@@ -34,6 +34,17 @@ cudaError_t dalloc(T** p, size_t count) {
     return e;
 }
 
+// Peer-visible arrays come out of ONE allocation per rank (PeerLinks::arena): every rank carves it in the same
+// order with the same sizes, so a peer's copy of an array sits at the same offset of the peer's arena.
+template <class T>
+cudaError_t aalloc(mpsb_handle* h, T** p, size_t count) {
+    size_t bytes = (sizeof(T) * std::max<size_t>(count, 1) + 255) & ~(size_t) 255;
+    if (h->arena_used + bytes > h->arena_bytes) return cudaErrorMemoryAllocation;
+    *p = reinterpret_cast<T*>(h->arena + h->arena_used);
+    h->arena_used += bytes;
+    return cudaSuccess;
+}
+
 void derive(Params& P) {
     const mpsb_settings& s = P.s;
     double D  = (double) s.dim;
@@ -71,7 +82,12 @@ int check_flags(mpsb_handle* h) {
 }
 
 int fetch_stats(mpsb_handle* h) {
-    CK(h, cudaMemcpyAsync(&h->host_stats, h->P.stats, sizeof(DevStats), cudaMemcpyDeviceToHost, h->stream));
+    const DevStats* src = h->P.stats;
+    if (h->world > 1) { // every rank counted its own rows: combine (collective), leaving the per-rank struct untouched
+        if (int rc = mpsb_comm_combine_stats(h)) return rc;
+        src = h->P.stats_all + MPSB_MAX_RANKS;
+    }
+    CK(h, cudaMemcpyAsync(&h->host_stats, src, sizeof(DevStats), cudaMemcpyDeviceToHost, h->stream));
     CK(h, cudaStreamSynchronize(h->stream));
     CK(h, cudaGetLastError());
     return MPSB_OK;
@@ -175,13 +191,31 @@ int mpsb_create(const mpsb_settings* settings, int64_t n, const int32_t* type, c
     for (auto& ev : h->ev) CKC(cudaEventCreate(&ev));
     size_t N = (size_t) P.Np, KN = (size_t) P.K * N; // row arrays padded to whole slices
     Sorted& S = P.S;
-    double** sd[] = {&S.x, &S.y, &S.z, &S.u, &S.v, &S.w, &S.u2, &S.v2, &S.w2, &S.ax, &S.ay, &S.az, &S.p, &S.minp, &S.ratio};
+    double** sd[] = {&S.x, &S.y, &S.z, &S.u, &S.v, &S.w, &S.u2, &S.v2, &S.w2, &S.ax, &S.ay, &S.az, &S.minp, &S.ratio};
     for (double** p : sd) CKC(dalloc(p, N));
-    CKC(dalloc(&S.type, N)); CKC(dalloc(&S.bc, N)); CKC(dalloc(&S.id, N));
+    CKC(dalloc(&S.type, N)); CKC(dalloc(&S.id, N));
     Home& H = P.H;
-    CKC(dalloc(&H.pos, 3 * N)); CKC(dalloc(&H.vel, 3 * N)); CKC(dalloc(&H.acc, 3 * N));
-    CKC(dalloc(&H.p, N)); CKC(dalloc(&H.minp, N)); CKC(dalloc(&H.ratio, N));
-    CKC(dalloc(&H.type, N)); CKC(dalloc(&H.bc, N)); CKC(dalloc(&H.inv, N));
+    P.cand_cap = 1024;
+    while ((size_t) P.cand_cap < N / 4) P.cand_cap <<= 1;
+    P.crec_seg = std::min(P.cand_cap / MPSB_MAX_RANKS, 16384); // per-rank segment of the collision-record inbox (multi-GPU)
+    // the arena: HOME, the halo fields S.bc / S.p, Dirichlet reach flags, collision records (see PeerLinks)
+    h->arena_bytes = (size_t) 256 * 16 + N * (3 * 3 * sizeof(double) + 3 * sizeof(double) + 2 * sizeof(int) + sizeof(int) +
+                                              sizeof(double) + sizeof(int)) +
+                     (size_t) P.crec_seg * MPSB_MAX_RANKS * sizeof(CollisionRecord) + 4096;
+    CKC(cudaMalloc((void**) &h->arena, h->arena_bytes));
+    CKC(cudaMemset(h->arena, 0, h->arena_bytes));
+    CKC(aalloc(h, &H.pos, 3 * N)); CKC(aalloc(h, &H.vel, 3 * N)); CKC(aalloc(h, &H.acc, 3 * N));
+    CKC(aalloc(h, &H.p, N)); CKC(aalloc(h, &H.minp, N)); CKC(aalloc(h, &H.ratio, N));
+    CKC(aalloc(h, &H.type, N)); CKC(aalloc(h, &H.bc, N));
+    CKC(aalloc(h, &S.bc, N)); CKC(aalloc(h, &S.p, N)); CKC(aalloc(h, &P.reach, N));
+    CKC(aalloc(h, &P.crec, (size_t) P.crec_seg * MPSB_MAX_RANKS)); CKC(aalloc(h, &P.crec_count, MPSB_MAX_RANKS));
+    P.L.arena = h->arena;
+    CKC(dalloc(&H.inv, N)); CKC(dalloc(&H.inv_alt, N));
+    CKC(dalloc(&P.keyrow, N)); CKC(dalloc(&P.ext, 1)); CKC(dalloc(&P.dflags, 2));
+    CKC(dalloc(&P.cstate, (size_t) 6 * 2 * P.crec_seg * MPSB_MAX_RANKS)); CKC(dalloc(&P.stats_all, MPSB_MAX_RANKS + 1)); // [MAX] = the combined struct
+    P.row_lo = 0;
+    P.row_hi = P.Np;
+    h->home_current = true;
     CKC(dalloc(&P.key, N)); CKC(dalloc(&P.key_alt, N)); CKC(dalloc(&P.val, N)); CKC(dalloc(&P.val_alt, N));
     CKC(dalloc(&P.cell_start, (size_t) P.numCells)); CKC(dalloc(&P.cell_end, (size_t) P.numCells));
     CKC(dalloc(&P.nbr_count, N)); CKC(dalloc(&P.nbr_idx, KN)); CKC(dalloc(&P.nbr_dist, KN));
@@ -190,8 +224,6 @@ int mpsb_create(const mpsb_settings* settings, int64_t n, const int32_t* type, c
     CKC(dalloc(&P.diag, N)); CKC(dalloc(&P.rhs, N));
     CKC(dalloc(&P.cg_r, N)); CKC(dalloc(&P.cg_p, N)); CKC(dalloc(&P.cg_ap, N)); CKC(dalloc(&P.cg_invdiag, N));
     CKC(dalloc(&P.parent, N)); CKC(dalloc(&P.mark, N));
-    P.cand_cap = 1024;
-    while ((size_t) P.cand_cap < N / 4) P.cand_cap <<= 1;
     CKC(dalloc(&P.cand, (size_t) P.cand_cap)); CKC(dalloc(&P.cand_count, 1));
     P.ev_cap = 4096;
     CKC(dalloc(&P.ev_ghost_id, (size_t) P.ev_cap)); CKC(dalloc(&P.ev_ghost_xyz, 3 * (size_t) P.ev_cap));
@@ -245,8 +277,8 @@ int mpsb_destroy(mpsb_handle* h) {
     Params& P = h->P;
     Sorted& S = P.S;
     Home& H   = P.H;
-    void* ptrs[] = {S.x, S.y, S.z, S.u, S.v, S.w, S.u2, S.v2, S.w2, S.ax, S.ay, S.az, S.p, S.minp, S.ratio, S.type,
-                    S.bc, S.id, H.pos, H.vel, H.acc, H.p, H.minp, H.ratio, H.type, H.bc, H.inv, P.key, P.key_alt,
+    void* ptrs[] = {S.x, S.y, S.z, S.u, S.v, S.w, S.u2, S.v2, S.w2, S.ax, S.ay, S.az, S.minp, S.ratio, S.type,
+                    S.id, h->arena, H.inv, H.inv_alt, P.keyrow, P.ext, P.dflags, P.cstate, P.stats_all, P.key, P.key_alt,
                     P.val, P.val_alt, P.cell_start, P.cell_end, P.nbr_count, P.nbr_idx, P.nbr_dist, P.ell_count,
                     P.ell_width, P.ell_cmin, P.ell_cmax, P.ell_col, P.ell_col16, P.ell_wide, P.ell_val, P.diag, P.rhs, P.cg_r, P.cg_p, P.cg_ap, P.cg_invdiag, P.cg_partials, P.cg_slice_pap, P.cluster_done, P.row_xy,
                     P.parent, P.mark, P.cand, P.cand_count, P.ev_ghost_id, P.ev_ghost_xyz, P.ev_uncon_id, P.stats,
@@ -264,6 +296,7 @@ int mpsb_upload(mpsb_handle* h, uint32_t mask, const mpsb_fields* f) {
     if (!h || !f) return MPSB_ERR_ARG;
     if (h->sticky) return h->sticky;
     CK(h, cudaSetDevice(h->device));
+    if (int rc = mpsb_comm_sync_home(h)) return rc; // several ranks: collective; fields not uploaded keep their latest values
     size_t N = (size_t) h->P.N;
     Home& H  = h->P.H;
     cudaStream_t st = h->stream;
@@ -278,7 +311,8 @@ int mpsb_upload(mpsb_handle* h, uint32_t mask, const mpsb_fields* f) {
     UP(MPSB_F_NUMBER_DENSITY_RATIO, H.ratio, f->number_density_ratio, sizeof(double) * N);
     UP(MPSB_F_BOUNDARY_CONDITION, H.bc, f->boundary_condition, sizeof(int) * N);
 #undef UP
-    if (h->have_lists && N > 0) mpsb_launch_gather_all(h); // keep the sorted working set in step
+    if (h->have_lists && N > 0) mpsb_launch_gather_all(h); // keep the sorted working set in step (every row, on every rank)
+    h->home_current = true;
     CK(h, cudaStreamSynchronize(st));
     return MPSB_OK;
 }
@@ -287,12 +321,14 @@ int mpsb_upload_device(mpsb_handle* h, const int32_t* d_type, const double* d_po
     if (!h) return MPSB_ERR_ARG;
     if (h->sticky) return h->sticky;
     CK(h, cudaSetDevice(h->device));
+    if (int rc = mpsb_comm_sync_home(h)) return rc;
     size_t N = (size_t) h->P.N;
     Home& H  = h->P.H;
     if (d_type) CK(h, cudaMemcpyAsync(H.type, d_type, sizeof(int) * N, cudaMemcpyDeviceToDevice, h->stream));
     if (d_position) CK(h, cudaMemcpyAsync(H.pos, d_position, sizeof(double) * 3 * N, cudaMemcpyDeviceToDevice, h->stream));
     if (d_velocity) CK(h, cudaMemcpyAsync(H.vel, d_velocity, sizeof(double) * 3 * N, cudaMemcpyDeviceToDevice, h->stream));
     if (h->have_lists && N > 0) mpsb_launch_gather_all(h);
+    h->home_current = true;
     CK(h, cudaStreamSynchronize(h->stream));
     return MPSB_OK;
 }
@@ -301,6 +337,7 @@ int mpsb_download(mpsb_handle* h, uint32_t mask, const mpsb_fields* f) {
     if (!h || !f) return MPSB_ERR_ARG;
     if (h->sticky) return h->sticky;
     CK(h, cudaSetDevice(h->device));
+    if (int rc = mpsb_comm_sync_home(h)) return rc; // several ranks: collective (every rank calls download at the same point)
     size_t N = (size_t) h->P.N;
     Home& H  = h->P.H;
     cudaStream_t st = h->stream;
@@ -345,11 +382,7 @@ static int issue_step(mpsb_handle* h, int want_number_density, bool timed) {
     mpsb_launch_matrix(h);
     mpsb_launch_dirichlet(h);
     EV(6);
-    mpsb_launch_pcg(h);
-    if (h->world > 1 && mpsb_comm_gather_pressure(h)) {
-        h->in_step = 0;
-        return h->sticky;
-    }
+    mpsb_launch_pcg(h);                              // several ranks: the halo pressures travel in pressure_post
     EV(7);
     mpsb_launch_pressure_post(h);
     mpsb_launch_gradient_move(h);                    // calcPressureGradient, moveParticlesWithPressureGradient
@@ -364,7 +397,7 @@ static int issue_step(mpsb_handle* h, int want_number_density, bool timed) {
     EV(10);
 #undef EV
     h->in_step = 0;
-    return MPSB_OK;
+    return h->sticky ? h->sticky : MPSB_OK; // a failed exchange (NCCL) inside a launcher is sticky
 }
 
 // Small cases are launch-bound (about 57 launches of a few microseconds each): the whole step is captured
@@ -479,7 +512,6 @@ int mpsb_run_phase(mpsb_handle* h, int phase, mpsb_step_stats* stats) {
     case MPSB_PH_DIRICHLET: mpsb_launch_dirichlet(h); break;
     case MPSB_PH_SOLVE:
         mpsb_launch_pcg(h);
-        if (h->world > 1 && mpsb_comm_gather_pressure(h)) return h->sticky;
         break;
     case MPSB_PH_PRESSURE_POST: mpsb_launch_pressure_post(h); break;
     case MPSB_PH_GRADIENT_MOVE:
@@ -503,6 +535,10 @@ int mpsb_run_phase(mpsb_handle* h, int phase, mpsb_step_stats* stats) {
 int mpsb_get_neighbors(mpsb_handle* h, int64_t* row_start, int32_t* ids, double* dist, int64_t capacity,
                        int64_t* total) {
     if (!h || !row_start || !total) return MPSB_ERR_ARG;
+    if (h->world > 1) {
+        snprintf(h->err, sizeof h->err, "mpsb_get_neighbors: inspection calls read one GPU's rows; not available on an attached handle");
+        return MPSB_ERR_ARG;
+    }
     if (h->sticky) return h->sticky;
     CK(h, cudaSetDevice(h->device));
     CK(h, cudaStreamSynchronize(h->stream));
@@ -544,6 +580,10 @@ int mpsb_get_neighbors(mpsb_handle* h, int64_t* row_start, int32_t* ids, double*
 int mpsb_get_ppe(mpsb_handle* h, int64_t* row_start, int32_t* col, double* val, double* rhs, int64_t capacity,
                  int64_t* nnz) {
     if (!h || !row_start || !nnz) return MPSB_ERR_ARG;
+    if (h->world > 1) {
+        snprintf(h->err, sizeof h->err, "mpsb_get_ppe: inspection calls read one GPU's rows; not available on an attached handle");
+        return MPSB_ERR_ARG;
+    }
     if (h->sticky) return h->sticky;
     CK(h, cudaSetDevice(h->device));
     CK(h, cudaStreamSynchronize(h->stream));

@@ -24,6 +24,7 @@ struct NcclApi {
     ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int)                                 = nullptr;
     ncclResult_t (*CommDestroy)(ncclComm_t)                                                           = nullptr;
     ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t)   = nullptr;
+    ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
     const char* (*GetErrorString)(ncclResult_t)                                                       = nullptr;
     bool ok = false;
 };
@@ -41,8 +42,9 @@ NcclApi& nccl() {
     api.CommInitRank   = (decltype(api.CommInitRank)) dlsym(api.dl, "ncclCommInitRank");
     api.CommDestroy    = (decltype(api.CommDestroy)) dlsym(api.dl, "ncclCommDestroy");
     api.AllGather      = (decltype(api.AllGather)) dlsym(api.dl, "ncclAllGather");
+    api.AllReduce      = (decltype(api.AllReduce)) dlsym(api.dl, "ncclAllReduce");
     api.GetErrorString = (decltype(api.GetErrorString)) dlsym(api.dl, "ncclGetErrorString");
-    api.ok = api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.AllGather && api.GetErrorString;
+    api.ok = api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.AllGather && api.AllReduce && api.GetErrorString;
     return api;
 }
 
@@ -52,6 +54,7 @@ struct MpsbComm {
     void* staging   = nullptr;                 // device buffer for the handle all-gather
     void* peer_inbox[MPSB_MAX_RANKS] = {};     // cudaIpcOpenMemHandle mappings (null for the own rank)
     void* peer_p[MPSB_MAX_RANKS]     = {};
+    void* peer_arena[MPSB_MAX_RANKS] = {};
 };
 
 constexpr size_t INBOX_BYTES = 4096;
@@ -63,6 +66,7 @@ constexpr size_t INBOX_EPOCH  = INBOX_ARRIVE + 64;
 struct HandlePair {
     cudaIpcMemHandle_t inbox;
     cudaIpcMemHandle_t p;
+    cudaIpcMemHandle_t arena;
 };
 
 int fail(mpsb_handle* h, const char* what, const char* detail) {
@@ -119,6 +123,7 @@ extern "C" int mpsb_attach_comm(mpsb_handle* h, int rank, int world_size, const 
     HandlePair mine;
     CKA(cudaIpcGetMemHandle(&mine.inbox, C->inbox));
     CKA(cudaIpcGetMemHandle(&mine.p, P.cg_p));
+    CKA(cudaIpcGetMemHandle(&mine.arena, h->arena));
     CKA(cudaMemcpy((char*) C->staging + sizeof(HandlePair) * rank, &mine, sizeof mine, cudaMemcpyHostToDevice));
     CKA(cudaStreamSynchronize(h->stream));
     // the all-gather also orders every rank's inbox memset before any peer's first remote store
@@ -129,14 +134,18 @@ extern "C" int mpsb_attach_comm(mpsb_handle* h, int rank, int world_size, const 
     CKA(cudaMemcpy(all, C->staging, sizeof(HandlePair) * world_size, cudaMemcpyDeviceToHost));
     PeerLinks& L = P.L;
     memset(&L, 0, sizeof L);
+    L.arena = h->arena;
     for (int q = 0; q < world_size; q++) {
-        void *ib = C->inbox, *pp = P.cg_p;
+        void *ib = C->inbox, *pp = P.cg_p, *ar = h->arena;
         if (q != rank) {
             CKA(cudaIpcOpenMemHandle(&C->peer_inbox[q], all[q].inbox, cudaIpcMemLazyEnablePeerAccess));
             CKA(cudaIpcOpenMemHandle(&C->peer_p[q], all[q].p, cudaIpcMemLazyEnablePeerAccess));
+            CKA(cudaIpcOpenMemHandle(&C->peer_arena[q], all[q].arena, cudaIpcMemLazyEnablePeerAccess));
             ib = C->peer_inbox[q];
             pp = C->peer_p[q];
+            ar = C->peer_arena[q];
         }
+        L.peer_arena[q] = (char*) ar;
         L.peer_red[q]  = (double*) ((char*) ib + INBOX_RED);
         L.peer_flag[q] = (unsigned long long*) ((char*) ib + INBOX_FLAG);
         L.peer_p[q]    = (double*) pp;
@@ -149,24 +158,73 @@ extern "C" int mpsb_attach_comm(mpsb_handle* h, int rank, int world_size, const 
     L.world  = world_size;
     h->rank  = rank;
     h->world = world_size;
+    // slab decomposition: this rank's fixed block of SORTED rows. The state uploaded so far is complete on every
+    // rank (mpsb_create took the whole arrays and built the lists for all rows), so HOME is current.
+    P.row_lo = rank * (P.Np / world_size);
+    P.row_hi = P.row_lo + P.Np / world_size;
+    h->home_current = true;
 #undef CKA
 #undef CKN
     return MPSB_OK;
 }
 
-// After the solve every rank holds its own row block of the pressure; the rest of the step works on the
-// whole vector, so the blocks are all-gathered in place over NCCL.
-int mpsb_comm_gather_pressure(mpsb_handle* h) {
-    if (!h->comm || h->world <= 1) return MPSB_OK;
+namespace {
+int nccl_fail(mpsb_handle* h, const char* what, ncclResult_t r) {
+    snprintf(h->err, sizeof h->err, "%s: %s", what, nccl().GetErrorString(r));
+    h->sticky = MPSB_ERR_COMM;
+    return MPSB_ERR_COMM;
+}
+template <class T>
+int gather_rows(mpsb_handle* h, T* field, size_t per_row, const char* what) {
     MpsbComm* C = (MpsbComm*) h->comm;
-    NcclApi& N  = nccl();
+    size_t bytes = (size_t) (h->P.Np / h->world) * per_row * sizeof(T);
+    ncclResult_t r = nccl().AllGather((char*) field + bytes * h->rank, field, bytes, ncclChar, C->comm, h->stream);
+    return r == ncclSuccess ? MPSB_OK : nccl_fail(h, what, r);
+}
+} // namespace
+
+// The cell keys every rank computed for its own rows of the OLD order -> the whole array on every rank (4 B per
+// particle: the sort of (key, id) pairs is replicated, everything else of the build is not).
+int mpsb_comm_allgather_keyrow(mpsb_handle* h) { return gather_rows(h, h->P.keyrow, 1, "ncclAllGather(keyrow)"); }
+
+// Make HOME current on every rank (before a download or a partial upload): all-gather the row blocks of every SORTED
+// field in place, then SORTED -> HOME for all rows. Collective: every rank calls it at the same point.
+int mpsb_comm_sync_home(mpsb_handle* h) {
+    if (h->world <= 1 || h->home_current) return MPSB_OK;
+    Sorted& S = h->P.S;
+    double* d[] = {S.x, S.y, S.z, S.u, S.v, S.w, S.ax, S.ay, S.az, S.p, S.minp, S.ratio};
+    for (double* f : d)
+        if (int rc = gather_rows(h, f, 1, "ncclAllGather(state)")) return rc;
+    if (int rc = gather_rows(h, S.type, 1, "ncclAllGather(type)")) return rc;
+    if (int rc = gather_rows(h, S.bc, 1, "ncclAllGather(bc)")) return rc;
+    mpsb_launch_scatter_all_rows(h);
+    h->home_current = true;
+    return MPSB_OK;
+}
+
+// Counters of the step: every rank counted its own rows; all-gather the structs and combine (k_halo.cu).
+void mpsb_launch_combine_stats(mpsb_handle* h);
+int mpsb_comm_combine_stats(mpsb_handle* h) {
+    if (h->world <= 1) return MPSB_OK;
+    MpsbComm* C = (MpsbComm*) h->comm;
     Params& P   = h->P;
-    size_t rows = (size_t) (P.Np / h->world);
-    ncclResult_t r = N.AllGather(P.S.p + rows * h->rank, P.S.p, rows, ncclDouble, C->comm, h->stream);
-    if (r != ncclSuccess) {
-        snprintf(h->err, sizeof h->err, "ncclAllGather(pressure): %s", N.GetErrorString(r));
-        h->sticky = MPSB_ERR_COMM;
-        return MPSB_ERR_COMM;
+    cudaMemcpyAsync(P.stats_all + h->rank, P.stats, sizeof(DevStats), cudaMemcpyDeviceToDevice, h->stream);
+    ncclResult_t r = nccl().AllGather(P.stats_all + h->rank, P.stats_all, sizeof(DevStats), ncclChar, C->comm, h->stream);
+    if (r != ncclSuccess) return nccl_fail(h, "ncclAllGather(stats)", r);
+    mpsb_launch_combine_stats(h);
+    return MPSB_OK;
+}
+
+// Dirichlet fixpoint (k_pressure.cu): OR of the two flags over the ranks, read back by the host that drives the loop.
+int mpsb_comm_allreduce_dflags(mpsb_handle* h, int* host2) {
+    MpsbComm* C = (MpsbComm*) h->comm;
+    ncclResult_t r = nccl().AllReduce(h->P.dflags, h->P.dflags, 2, ncclInt, ncclMax, C->comm, h->stream);
+    if (r != ncclSuccess) return nccl_fail(h, "ncclAllReduce(dirichlet flags)", r);
+    if (cudaMemcpyAsync(host2, h->P.dflags, 2 * sizeof(int), cudaMemcpyDeviceToHost, h->stream) != cudaSuccess ||
+        cudaStreamSynchronize(h->stream) != cudaSuccess) {
+        snprintf(h->err, sizeof h->err, "Dirichlet fixpoint: flag read-back failed");
+        h->sticky = MPSB_ERR_CUDA;
+        return MPSB_ERR_CUDA;
     }
     return MPSB_OK;
 }
@@ -177,6 +235,7 @@ void mpsb_comm_release(mpsb_handle* h) {
     for (int q = 0; q < MPSB_MAX_RANKS; q++) {
         if (C->peer_inbox[q]) cudaIpcCloseMemHandle(C->peer_inbox[q]);
         if (C->peer_p[q]) cudaIpcCloseMemHandle(C->peer_p[q]);
+        if (C->peer_arena[q]) cudaIpcCloseMemHandle(C->peer_arena[q]);
     }
     if (C->comm && nccl().ok) nccl().CommDestroy(C->comm);
     if (C->staging) cudaFree(C->staging);

@@ -54,6 +54,7 @@ struct Home {
     double *p, *minp, *ratio;
     int *type, *bc;
     int *inv;                // particle id -> sorted index (valid after a build)
+    int *inv_alt;            // multi-GPU: the perm inverse being built while `inv` (the old one) is still read
 };
 
 // Multi-GPU view of the PPE solve (mpsb_comm.cu). One process per GPU; rank g owns the
@@ -74,6 +75,20 @@ struct PeerLinks {
     double* peer_red[MPSB_MAX_RANKS];
     unsigned long long* peer_flag[MPSB_MAX_RANKS];
     double* peer_p[MPSB_MAX_RANKS];
+    // the peer-visible ARENA (slab decomposition of the particle phases): one allocation per rank
+    // holding every array a peer stores into — HOME, the halo fields S.bc / S.p, the Dirichlet reach flags and the
+    // collision-record inbox. All ranks carve it identically, so peer q's copy of a local arena pointer x is
+    // peer_arena[q] + (x - arena).
+    char* arena;
+    char* peer_arena[MPSB_MAX_RANKS];
+};
+
+// Per-rank row extents, identical on every rank (computed from the replicated sorted keys by ext_kernel):
+// rows [own_lo, own_hi) are the rank's fixed block of the SORTED order; rows [ext_lo, ext_hi) additionally cover
+// its HALO: every row whose cell is within the 3x3(x3) stencil of a cell holding one of its active rows.
+struct RankExtents {
+    int own_lo[MPSB_MAX_RANKS], own_hi[MPSB_MAX_RANKS];
+    int ext_lo[MPSB_MAX_RANKS], ext_hi[MPSB_MAX_RANKS];
 };
 
 // Everything a kernel needs, passed by value.
@@ -131,7 +146,35 @@ struct Params {
     DevStats* stats;
     int* n_active; // == &stats->n_active
     PeerLinks L;
+    // ---- slab decomposition (world > 1; world == 1: row_lo = 0, row_hi = Np and none of the rest is touched) ----
+    int row_lo, row_hi;        // the SORTED rows this rank owns: every per-particle kernel covers exactly these
+    unsigned* keyrow;          // Np: cell key of every row of the OLD order (own block computed, the rest all-gathered)
+    RankExtents* ext;          // device copy of the extents of the current order
+    int* reach;                // Np (arena): Dirichlet marks of boundary rows, stored by their owners
+    int* dflags;               // 2: Dirichlet fixpoint: [0] a mark changed this round, [1] an own Inner row is still unmarked
+    struct CollisionRecord* crec;      // arena: W segments of crec_seg records, segment q written by rank q
+    int* crec_count;                   // arena: W counts
+    int crec_seg;
+    double* cstate;            // 6 * 2 * W * crec_seg: compact (x, y, z, u, v, w) of the particles the records touch
+    DevStats* stats_all;       // W: every rank's counters of the step (all-gathered, then combined into *stats)
 };
+
+// One collision candidate as it travels between ranks: the key fixes the reference's visiting order
+// ((id_i << 32) | list slot), the rest is the pre-collision snapshot the replay starts from.
+struct CollisionRecord {
+    unsigned long long key;
+    int row_i, row_j;
+    int type_j, pad;
+    double dist;
+    double xi[3], ui[3], xj[3], uj[3];
+};
+
+#ifdef __CUDACC__
+template <class T>
+__device__ __forceinline__ T* mpsb_peer(const Params& P, T* local, int q) {
+    return reinterpret_cast<T*>(P.L.peer_arena[q] + (reinterpret_cast<char*>(local) - P.L.arena));
+}
+#endif
 
 // One captured step (mpsb_api.cu): valid for the pointer state it was captured in.
 #define MPSB_MAX_STEP_GRAPHS 8
@@ -174,6 +217,8 @@ struct mpsb_handle {
     int* block_hist; int block_hist_cap;
     unsigned long long* scan_status; int scan_status_cap; // look-back scan: one status word per scan tile, then the ticket counter
     void* comm; int rank, world; // multi-GPU (mpsb_comm.cu): MpsbComm*, mirrors P.L.rank / P.L.world
+    char* arena; size_t arena_bytes, arena_used; // peer-visible arrays (PeerLinks::arena)
+    bool home_current;      // multi-GPU: HOME holds the latest state of EVERY particle (after an upload / a collective sync)
     // host staging for inspection calls
 };
 
@@ -196,8 +241,24 @@ int mpsb_pcg_configure(mpsb_handle* h);
 void mpsb_launch_spmv_probe(mpsb_handle* h, int matrix_free); // diagnostic: one sweep A, cg_p -> cg_ap
 int mpsb_pcg_cluster_configure(mpsb_handle* h);         // k_pcg_cluster.cu
 int mpsb_launch_pcg_cluster(mpsb_handle* h);
-int mpsb_comm_gather_pressure(mpsb_handle* h);          // mpsb_comm.cu: all-gather the solved row blocks of p
 void mpsb_comm_release(mpsb_handle* h);
+// ---- slab decomposition (world > 1) ----
+int mpsb_comm_allgather_keyrow(mpsb_handle* h);         // mpsb_comm.cu: NCCL all-gather of the own-block cell keys
+int mpsb_comm_sync_home(mpsb_handle* h);                // all-gather every SORTED field, then SORTED -> HOME for all rows
+int mpsb_comm_combine_stats(mpsb_handle* h);            // all-gather DevStats, combine into *P.stats
+int mpsb_comm_allreduce_dflags(mpsb_handle* h, int* host2); // Dirichlet fixpoint: OR of the two flags over the ranks
+void mpsb_launch_xbarrier(mpsb_handle* h);              // k_halo.cu: cross-rank barrier on the stream (epoch flags in the inboxes)
+void mpsb_launch_halo_push_bc(mpsb_handle* h);          // own rows inside a peer's extent -> that peer's S.bc
+void mpsb_launch_halo_push_p(mpsb_handle* h);           // ... -> that peer's S.p
+void mpsb_launch_scatter_all_rows(mpsb_handle* h);      // SORTED -> HOME for every row (after mpsb_comm_sync_home's gathers)
+static inline int mpsb_own_rows(const mpsb_handle* h) { // rows a per-particle kernel of this rank covers (< N)
+    int hi = h->P.row_hi < h->P.N ? h->P.row_hi : h->P.N;
+    return hi > h->P.row_lo ? hi - h->P.row_lo : 0;
+}
+static inline int mpsb_own_grid(const mpsb_handle* h, int block) {
+    int r = mpsb_own_rows(h);
+    return r > 0 ? (r + block - 1) / block : 1;
+}
 
 #define MPSB_LAUNCH(h, kernel, grid, block, smem, ...)                                   \
     do {                                                                                 \

@@ -70,7 +70,8 @@ def _gpu_count():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("case,steps", [("dambreak", 6), ("dambreak_fine", 4), ("nx=400", 2)])
+@pytest.mark.parametrize("case,steps", [("dambreak", 6), ("dambreak@200", 50), ("dambreak@320", 8), ("dambreak_fine", 4),
+                                        ("nx=400", 2), ("nx=800", 1)])
 def test_split_solve_matches_single_gpu(case, steps):
     n = _gpu_count()
     if n < 2:
@@ -84,7 +85,13 @@ def test_split_solve_matches_single_gpu(case, steps):
     lines = [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
     assert r.returncode == 0 and lines, r.stdout[-2000:] + r.stderr[-2000:]
     rep = json.loads(lines[-1])
-    assert rep["ok"] and rep["ranks_bit_identical"] and rep["flags_equal"], rep
+    assert rep["ok"] and rep["ranks_bit_identical"] and rep["flags_equal"] and rep["counters_equal"], rep
+    if case == "dambreak@200":
+        assert rep["collisions_replayed"] > 0, rep  # the cross-rank collision replay really ran
+    if case == "dambreak@320":
+        assert rep["particles_ghosted"] > 0, rep
+    if case.startswith("nx="):
+        assert rep["vs_compiled_reference"]["ok"], rep
 
 
 @pytest.mark.gpu
