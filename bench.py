@@ -310,6 +310,46 @@ def other_configs(gpu_steps, with_cpu=True, cpu_seconds=1.5):
             row["cpu_threads_all"] = cpu_threads()
             row["speedup_vs_best_cpu"] = min(row["cpu_ms_per_step_1_thread"], row["cpu_ms_per_step_all_threads"]) / row["gpu_ms_per_step"]
         rows.append(row)
+    # a 3-D case at a size where bandwidth starts to matter (the reference ships none): the generated
+    # open tank of tests/golden/tank3d_*, 4x finer (radius ratio 2.1 -> ~120 neighbours, K = 384 slots)
+    import tempfile
+
+    S, t, p, v = C.tank3d(n_fluid=(32, 40, 24), n_tank=(64, 56, 24), jitter=0.05)
+    n = int(np.count_nonzero(t != C.GHOST))
+    dev = capi.DeviceMPS(S, t, p, v)
+    dev.load_initial_state()
+    for _ in range(3):
+        dev.step_forward(False)
+    steps3 = max(5, gpu_steps // 10)
+    its, solve, tot = [], [], []
+    t0 = time.perf_counter()
+    for _ in range(steps3):
+        dev.step_forward(False)
+        st = dev.last_stats
+        its.append(st.cg_iterations)
+        solve.append(st.ms_solve)
+        tot.append(st.ms_total)
+    wall = time.perf_counter() - t0
+    row = {"config": "3-D (SURVEY 8 f-4, generated)", "case": "tank3d 64x56x24 cells, fluid 32x40x24", "particles": n,
+           "gpu_steps": steps3, "gpu_ms_per_step": 1e3 * wall / steps3, "gpu_particle_steps_per_s": n * steps3 / wall,
+           "gpu_solve_ms_per_step": float(np.mean(solve)), "cg_iterations_per_step": float(np.mean(its)),
+           "gpu_us_per_cg_iteration": 1e3 * float(np.sum(solve)) / max(1, int(np.sum(its))),
+           "max_neighbors": int(dev.last_stats.max_neighbors), "nnz": int(dev.last_stats.nnz)}
+    dev.close()
+    if with_cpu and R.have_ref():
+        yml = C.write_settings_yaml(S, os.path.join(tempfile.mkdtemp(prefix="mpsb_bench3d_"), "settings.yml"))
+        ref = R.RefMPS(yml, arrays=(t, p, v))
+        set_omp_threads(cpu_threads())
+        ref.step(False)
+        k, t0 = 0, time.perf_counter()
+        while k < 1 or time.perf_counter() - t0 < cpu_seconds:
+            ref.step(False)
+            k += 1
+        row["cpu_ms_per_step_all_threads"] = 1e3 * (time.perf_counter() - t0) / k
+        row["cpu_threads_all"] = cpu_threads()
+        row["speedup_vs_best_cpu"] = row["cpu_ms_per_step_all_threads"] / row["gpu_ms_per_step"]
+        ref.close()
+    rows.append(row)
     return rows
 
 

@@ -168,9 +168,16 @@ int mpsb_step(mpsb_handle* h, int want_number_density, mpsb_step_stats* stats);
 int mpsb_run_phase(mpsb_handle* h, int phase, mpsb_step_stats* stats);
 
 /* --- state transfer (host mirror of `std::vector<Particle>`, src/particle.hpp:21-46) ----- */
+/* With an attached multi-GPU group both calls are COLLECTIVE: every rank calls them at the same point of its program
+ * (the ranks first bring HOME up to date from each other's row blocks); each rank passes / receives whole arrays. */
 int mpsb_upload(mpsb_handle* h, uint32_t field_mask, const mpsb_fields* src);
 int mpsb_download(mpsb_handle* h, uint32_t field_mask, const mpsb_fields* dst);
 int64_t mpsb_num_particles(const mpsb_handle* h);
+
+/* Page-locked host memory for the buffers passed to mpsb_upload / mpsb_download (cudaHostAlloc: the copies then run
+ * as DMA at full PCIe rate with no staging copy inside the driver). Returns NULL on failure; free with mpsb_host_free. */
+void* mpsb_host_alloc(uint64_t bytes);
+void mpsb_host_free(void* p);
 
 /* --- inspection (parity tests) -------------------------------------------------------------
  * Neighbour lists of the last build as CSR by particle id, entries in the reference's order
@@ -186,8 +193,12 @@ int mpsb_get_ppe(mpsb_handle* h, int64_t* row_start, int32_t* col, double* val, 
  * kind 0 = ghosted (xyz = position at the time, 3 doubles each), 1 = Dirichlet-unconnected. */
 int mpsb_events(mpsb_handle* h, int kind, int32_t* ids, double* xyz, int capacity, int* count);
 
-/* --- multi-GPU (one process per GPU; slab/row partition) -------------------------------------
- * Attach an exchange group before the first step. `nccl_unique_id` is the 128-byte ncclUniqueId
+/* --- multi-GPU (one process per GPU; slab decomposition by rows of the cell-major order) ---------------------
+ * Attach an exchange group before the first step. From then on every rank runs every phase of the step on its own
+ * block of rows only (halo particles, particle migration, halo flags / pressures, collision records and the Krylov
+ * exchanges travel over NVLink peer memory; NCCL carries the 4-byte cell keys, the counters and state syncs).
+ * mpsb_step / mpsb_run_phase / mpsb_upload / mpsb_download are then collective; the inspection calls
+ * (mpsb_get_neighbors, mpsb_get_ppe, mpsb_debug_spmv) are single-GPU only; mpsb_events lists the calling rank's events. `nccl_unique_id` is the 128-byte ncclUniqueId
  * produced on rank 0 and distributed by the host (torch.distributed / a launcher). */
 int mpsb_comm_unique_id(void* out128);
 int mpsb_attach_comm(mpsb_handle* h, int rank, int world_size, const void* nccl_unique_id128);

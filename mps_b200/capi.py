@@ -27,7 +27,7 @@ EXPORTED = [
     "mpsb_create", "mpsb_destroy", "mpsb_last_error", "mpsb_version", "mpsb_step", "mpsb_run_phase",
     "mpsb_upload", "mpsb_download", "mpsb_num_particles", "mpsb_get_neighbors", "mpsb_get_ppe", "mpsb_events",
     "mpsb_comm_unique_id", "mpsb_attach_comm", "mpsb_upload_device", "mpsb_launch_count", "mpsb_set_stream",
-    "mpsb_debug_cg_cycles", "mpsb_debug_cg_block_cycles", "mpsb_debug_spmv",
+    "mpsb_debug_cg_cycles", "mpsb_debug_cg_block_cycles", "mpsb_debug_spmv", "mpsb_host_alloc", "mpsb_host_free",
 ]
 
 

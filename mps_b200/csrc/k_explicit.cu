@@ -20,6 +20,7 @@ __device__ __forceinline__ bool out_of_domain(const mpsb_settings& s, double x, 
 }
 
 __device__ __forceinline__ void ghost_event(const Params& P, int s, double x, double y, double z) {
+    mpsb_record_ghost_ratio(P, s);
     int e = atomicAdd(&P.stats->n_ghosted, 1);
     if (e < P.ev_cap) {
         P.ev_ghost_id[e]          = P.S.id[s];

@@ -95,11 +95,15 @@ __global__ void __launch_bounds__(128) neighbor_kernel(Params P) {
     if ((threadIdx.x & 31) == 0 && m > 0) atomicMax(&P.stats->max_neighbors, m);
 }
 
-// ratio = Surface ? 0 : n(re_p) / n0_p   (src/mps.cpp:630-640); ghosts keep their last value.
+// ratio = Surface ? 0 : n(re_p) / n0_p   (src/mps.cpp:630-640), Ghosts included (their list is frozen).
 __global__ void number_density_kernel(Params P) {
     int s = P.row_lo + blockIdx.x * blockDim.x + threadIdx.x; // own rows (one GPU: all of them)
     if (s >= P.row_hi) return;
-    if (s >= *P.n_active) return;
+    if (s >= P.N) return;
+    if (s >= *P.n_active) { // a Ghost: the sum over the list it had when it left (Params::ghost_ratio), 0 while flagged Surface
+        P.S.ratio[s] = P.S.bc[s] == MPSB_BC_SURFACE ? 0.0 : P.ghost_ratio[P.S.id[s]];
+        return;
+    }
     double ratio = 0.0;
     if (P.S.bc[s] != MPSB_BC_SURFACE) {
         const double re = P.s.re_pressure;
@@ -123,6 +127,18 @@ __global__ void number_density_kernel(Params P) {
 void mpsb_launch_neighbors(mpsb_handle* h) {
     Params& P = h->P;
     MPSB_LAUNCH(h, neighbor_kernel, mpsb_own_grid(h, 128), 128, 0, P);
+}
+
+namespace {
+__global__ void ghost_ratio_from_home_kernel(Params P) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < P.N && P.H.type[i] == MPSB_GHOST) P.ghost_ratio[i] = P.H.ratio[i];
+}
+} // namespace
+
+void mpsb_launch_ghost_ratio_from_home(mpsb_handle* h) {
+    Params& P = h->P;
+    MPSB_LAUNCH(h, ghost_ratio_from_home_kernel, mpsb_div_up(P.N, 256), 256, 0, P);
 }
 
 void mpsb_launch_number_density(mpsb_handle* h) {

@@ -199,15 +199,15 @@ int mpsb_create(const mpsb_settings* settings, int64_t n, const int32_t* type, c
     while ((size_t) P.cand_cap < N / 4) P.cand_cap <<= 1;
     P.crec_seg = std::min(P.cand_cap / MPSB_MAX_RANKS, 16384); // per-rank segment of the collision-record inbox (multi-GPU)
     // the arena: HOME, the halo fields S.bc / S.p, Dirichlet reach flags, collision records (see PeerLinks)
-    h->arena_bytes = (size_t) 256 * 16 + N * (3 * 3 * sizeof(double) + 3 * sizeof(double) + 2 * sizeof(int) + sizeof(int) +
-                                              sizeof(double) + sizeof(int)) +
+    h->arena_bytes = (size_t) 256 * 20 + N * (3 * 3 * sizeof(double) + 3 * sizeof(double) + 2 * sizeof(int) + sizeof(int) +
+                                              sizeof(double) + sizeof(int) + sizeof(double)) +
                      (size_t) P.crec_seg * MPSB_MAX_RANKS * sizeof(CollisionRecord) + 4096;
     CKC(cudaMalloc((void**) &h->arena, h->arena_bytes));
     CKC(cudaMemset(h->arena, 0, h->arena_bytes));
     CKC(aalloc(h, &H.pos, 3 * N)); CKC(aalloc(h, &H.vel, 3 * N)); CKC(aalloc(h, &H.acc, 3 * N));
     CKC(aalloc(h, &H.p, N)); CKC(aalloc(h, &H.minp, N)); CKC(aalloc(h, &H.ratio, N));
     CKC(aalloc(h, &H.type, N)); CKC(aalloc(h, &H.bc, N));
-    CKC(aalloc(h, &S.bc, N)); CKC(aalloc(h, &S.p, N)); CKC(aalloc(h, &P.reach, N));
+    CKC(aalloc(h, &S.bc, N)); CKC(aalloc(h, &S.p, N)); CKC(aalloc(h, &P.reach, N)); CKC(aalloc(h, &P.ghost_ratio, N));
     CKC(aalloc(h, &P.crec, (size_t) P.crec_seg * MPSB_MAX_RANKS)); CKC(aalloc(h, &P.crec_count, MPSB_MAX_RANKS));
     P.L.arena = h->arena;
     CKC(dalloc(&H.inv, N)); CKC(dalloc(&H.inv_alt, N));
@@ -311,6 +311,7 @@ int mpsb_upload(mpsb_handle* h, uint32_t mask, const mpsb_fields* f) {
     UP(MPSB_F_NUMBER_DENSITY_RATIO, H.ratio, f->number_density_ratio, sizeof(double) * N);
     UP(MPSB_F_BOUNDARY_CONDITION, H.bc, f->boundary_condition, sizeof(int) * N);
 #undef UP
+    if ((mask & (MPSB_F_NUMBER_DENSITY_RATIO | MPSB_F_TYPE)) && N > 0) mpsb_launch_ghost_ratio_from_home(h);
     if (h->have_lists && N > 0) mpsb_launch_gather_all(h); // keep the sorted working set in step (every row, on every rank)
     h->home_current = true;
     CK(h, cudaStreamSynchronize(st));
@@ -672,6 +673,19 @@ int mpsb_debug_spmv(mpsb_handle* h, const double* x, double* y, int matrix_free)
     CK(h, cudaMemcpy(ys.data(), P.cg_ap, sizeof(double) * (size_t) P.Np, cudaMemcpyDeviceToHost));
     for (size_t i = 0; i < N; i++) y[i] = bc[(size_t) inv[i]] == MPSB_BC_INNER ? ys[(size_t) inv[i]] : 0.0;
     return MPSB_OK;
+}
+
+void* mpsb_host_alloc(uint64_t bytes) {
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, (size_t) (bytes ? bytes : 1), cudaHostAllocDefault) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    return p;
+}
+
+void mpsb_host_free(void* p) {
+    if (p) cudaFreeHost(p);
 }
 
 int mpsb_set_stream(mpsb_handle* h, void* cuda_stream) {

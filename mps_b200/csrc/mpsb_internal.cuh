@@ -151,6 +151,9 @@ struct Params {
     unsigned* keyrow;          // Np: cell key of every row of the OLD order (own block computed, the rest all-gathered)
     RankExtents* ext;          // device copy of the extents of the current order
     int* reach;                // Np (arena): Dirichlet marks of boundary rows, stored by their owners
+    double* ghost_ratio;       // N (arena), by particle id: n(re_p) / n0 of the list a particle had when it turned Ghost. The
+                               // reference never clears a Ghost's list (setNeighbors skips it, src/mps.cpp:590-593), so its
+                               // setNumberDensity keeps reporting that sum (:630-640) — and Exporter::toVtu writes it
     int* dflags;               // 2: Dirichlet fixpoint: [0] a mark changed this round, [1] an own Inner row is still unmarked
     struct CollisionRecord* crec;      // arena: W segments of crec_seg records, segment q written by rank q
     int* crec_count;                   // arena: W counts
@@ -228,6 +231,7 @@ void mpsb_launch_gather_all(mpsb_handle* h);            // HOME -> SORTED with t
 void mpsb_launch_scatter_all(mpsb_handle* h);           // SORTED -> HOME
 void mpsb_launch_neighbors(mpsb_handle* h);             // k_neighbors.cu
 void mpsb_launch_number_density(mpsb_handle* h);
+void mpsb_launch_ghost_ratio_from_home(mpsb_handle* h); // after an upload: a Ghost's recorded sum is its uploaded ratio
 void mpsb_launch_explicit(mpsb_handle* h);              // k_explicit.cu
 void mpsb_launch_collision(mpsb_handle* h);
 void mpsb_launch_gradient_move(mpsb_handle* h);
@@ -307,4 +311,23 @@ __device__ __forceinline__ void mpsb_walk_list(const Params& P, int s, int cnt, 
     }
 }
 struct MpsbNoRec {};
+
+// A particle turns Ghost: record n(re_p) / n0 of the list it has NOW — the list the reference keeps for it from
+// then on (see Params::ghost_ratio) — on every rank (a Ghost's row ends up in the tail block, owned by another rank).
+__device__ __forceinline__ void mpsb_record_ghost_ratio(const Params& P, int s) {
+    const double re = P.s.re_pressure;
+    const int cnt = P.nbr_count[s];
+    double n = 0.0;
+    for (int k = 0; k < cnt; k++) {
+        const double d = P.nbr_dist[SELL(k, s)];
+        if (d < re) n += mpsb_weight(d, re);
+    }
+    const double v = n / P.s.n0_pressure;
+    const int id = P.S.id[s];
+    if (P.L.world <= 1) {
+        P.ghost_ratio[id] = v;
+    } else {
+        for (int q = 0; q < P.L.world; q++) mpsb_peer(P, P.ghost_ratio, q)[id] = v;
+    }
+}
 #endif

@@ -190,8 +190,8 @@ double MPS::loadInitialStateFromFile(const std::filesystem::path& statePath) {
     return time;
 }
 
-bool MPS::saveState(const std::filesystem::path& statePath, double time) {
-    downloadParticles();
+bool MPS::saveState(const std::filesystem::path& statePath, double time, bool download) {
+    if (download) downloadParticles();
     return state_io::write(statePath, time, particles);
 }
 
@@ -268,11 +268,21 @@ double MPS::stepForward(const bool isTimeToExport) {
 void MPS::downloadParticles() {
     if (!handle) return;
     const std::size_t n = particles.size();
-    std::vector<std::int32_t> type(n), bc(n);
-    std::vector<double> pos(3 * n), vel(3 * n), acc(3 * n), p(n), minp(n), ratio(n);
+    // one page-locked block, reused by every export (f-1: pinned D2H instead of pageable vectors): 12 doubles + 2 ints per particle
+    const std::size_t need = n * (12 * sizeof(double) + 2 * sizeof(std::int32_t)) + 64;
+    if (stagingBytes < need) {
+        staging.reset();
+        void* block = mpsb_host_alloc(need);
+        if (!block) fail("mpsb_host_alloc (pinned staging)", MPSB_ERR_CUDA);
+        staging      = std::shared_ptr<void>(block, [](void* p) { mpsb_host_free(p); });
+        stagingBytes = need;
+    }
+    double* d = static_cast<double*>(staging.get());
+    double *pos = d, *vel = d + 3 * n, *acc = d + 6 * n, *p = d + 9 * n, *minp = d + 10 * n, *ratio = d + 11 * n;
+    std::int32_t *type = reinterpret_cast<std::int32_t*>(d + 12 * n), *bc = type + n;
     mpsb_fields f;
-    f.type = type.data(); f.position = pos.data(); f.velocity = vel.data(); f.acceleration = acc.data();
-    f.pressure = p.data(); f.minimum_pressure = minp.data(); f.number_density_ratio = ratio.data(); f.boundary_condition = bc.data();
+    f.type = type; f.position = pos; f.velocity = vel; f.acceleration = acc;
+    f.pressure = p; f.minimum_pressure = minp; f.number_density_ratio = ratio; f.boundary_condition = bc;
     int rc = mpsb_download(handle.get(), MPSB_F_ALL, &f);
     if (rc != MPSB_OK) fail("mpsb_download", rc);
     for (std::size_t i = 0; i < n; i++) {

@@ -62,7 +62,8 @@ public:
     // velocity and the derived fields a following step can depend on (pressure, number-density ratio, flags),
     // so save + load + continue equals an uninterrupted run bit for bit. Returns the file's time.
     double loadInitialStateFromFile(const std::filesystem::path& statePath);
-    bool saveState(const std::filesystem::path& statePath, double time); // downloads first
+    // downloads first unless told the particles are current (multi-GPU: the download is collective, the write is rank 0's)
+    bool saveState(const std::filesystem::path& statePath, double time, bool download = true);
     int device = 0; // CUDA device ordinal used by loadInitialState (MPSB_DEVICE overrides)
     // Multi-GPU: one process per GPU. With WORLD_SIZE > 1 in the environment (rendezvous.hpp) the ranks split the
     // PPE solve; every rank holds the whole particle set and returns identical results.
@@ -82,6 +83,9 @@ private:
     // shared_ptr: the reference's driver copy-assigns `mps = MPS(path)` (src/simulation.cpp:33); copies
     // share the device state, the last owner destroys it.
     std::shared_ptr<mpsb_handle> handle;
+    // page-locked staging for downloadParticles (mpsb_host_alloc): allocated once, DMA target of mpsb_download
+    std::shared_ptr<void> staging;
+    std::size_t stagingBytes = 0;
 
     double importInitialCondition(); // reference src/mps.cpp:38-94
     void createDeviceState(bool restoreDerived = false);

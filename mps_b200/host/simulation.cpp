@@ -68,7 +68,10 @@ void Simulation::run(const fs::path& inputYamlPath) {
         timeStep++;
     }
     simulationEndTime = system_clock::now();
-    if (writer && !stateOut.empty() && !mps.saveState(stateOut, time)) mpslog::error("Could not write the state file: " + stateOut.string());
+    if (!stateOut.empty()) { // the download is collective with several ranks (every rank joins); rank 0 alone writes
+        mps.downloadParticles();
+        if (writer && !mps.saveState(stateOut, time, false)) mpslog::error("Could not write the state file: " + stateOut.string());
+    }
     endSimulation();
 }
 
