@@ -17,6 +17,8 @@
  *   MPSB_CG_ITERATION_CAP=<n>    stop the solve after n iterations (profiling a bounded solve)
  *   MPSB_MATRIX_FREE=0|1         sweep A of the grid solve streams the stored off-diagonals (0) or recomputes them from
  *                                positions (1; 2-D cases only)
+ *   MPSB_L2_RESIDENT_KB=<kb>     L2 policy of the solve's matrix stream: <kb> KiB travel as evict_last, the rest as evict_first
+ *                                (default 16384; 0 = no policy), for row blocks of at most MPSB_L2_MAX_ROWS rows (2 500 000)
  * and by the host mirror (mps_b200/host): MPSB_DEVICE=<ordinal>, MPSB_CSV_FLOAT=gcc5.
  *
  * Particle arrays are SoA, indexed by particle id (the reference assumes id == index,

@@ -16,8 +16,10 @@
 //                                       copies (cp.async.bulk + mbarrier), one ring of stages per warp,
 //                                       so the bytes in flight do not depend on registers/occupancy;
 //                                       p[col] gathers are served by L1/L2 (p is 8n bytes, L2-resident)
-//   sweep B  x += a p; r -= a ap; |r|^2, r.z   read x,p,r,ap,invdiag, write x,r = 56n   (16-byte vectors)
-//   sweep C  p = z + b p (z = invdiag r)       read r,invdiag,p, write p = 32n
+//   sweep B  r -= a ap; |r|^2, r.z              read r,ap,invdiag, write r = 32n        (16-byte vectors)
+//   sweep C  x += a p; p = z + b p (z = invdiag r)   read x,r,invdiag,p, write x,p = 48n
+//            (x += a p rides in sweep C, which holds p in registers anyway: 8n bytes fewer per iteration than the
+//            textbook placement in sweep B — 80n instead of the 88n the algorithmic figure counts; same operands, same rounding)
 // = 12 nnz + 108 n algorithmic bytes, the figure bench.py's roofline uses.
 //
 // Multi-GPU (template MULTI): rank g solves the rows of its y-slab (a contiguous block of
@@ -67,6 +69,17 @@ namespace cg = cooperative_groups;
 #endif
 #ifndef MPSB_MATRIX_FREE_DEFAULT
 #define MPSB_MATRIX_FREE_DEFAULT 0 // sweep A recomputes off-diagonals from positions (see spmv_sweep_mf); env MPSB_MATRIX_FREE overrides
+#endif
+// L2 policy of the matrix stream (L2Plan): on for row blocks of up to MPSB_L2_MAX_ROWS rows — the sizes whose five CG
+// vectors (40 B per row) fit the L2 next to the stream; measured neutral-to-negative above (4 M rows on one GPU)
+#ifndef MPSB_L2_RESIDENT_KB_DEFAULT
+#define MPSB_L2_RESIDENT_KB_DEFAULT 16384
+#endif
+#ifndef MPSB_L2_MAX_ROWS_DEFAULT
+#define MPSB_L2_MAX_ROWS_DEFAULT 2500000
+#endif
+#ifndef PCG_SLICE_SUM_MAX
+#define PCG_SLICE_SUM_MAX 40960 // several GPUs: blocks of up to this many slices sum p.Ap in the exchange's last CTA (no grid barrier)
 #endif
 #ifndef PCG_SPLIT_SYNC
 #define PCG_SPLIT_SYNC 0 // diagnostic: book the barrier/exchange after sweep B under B and after sweep C under C
@@ -137,6 +150,14 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned by
                  "l"(src), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
 #endif
+}
+// the same with an L2 eviction-priority policy chosen at run time (resident part of the matrix: evict_last, the rest:
+// evict_first — see L2Plan)
+__device__ __forceinline__ void bulk_g2s_pol(void* dst, const void* src, unsigned bytes, unsigned long long* bar, unsigned long long pol) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(
+                     smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(pol)
+                 : "memory");
 }
 // 16-byte accesses of the vector sweeps, optionally tagged "last to go" in L2 (PCG_VEC_HINT)
 __device__ __forceinline__ double2 ld2_keep(const double* base, int i) {
@@ -248,7 +269,11 @@ struct Xchg {
 //       with release.sys, readers poll it with acquire.sys.
 // It subsumes a grid-wide barrier. A rank that never arrives (crashed peer) trips the timeout -> trap,
 // which fails the launch loudly instead of hanging the box.
-enum { XCHG_SUM = 0, XCHG_MINMAX = 1, XCHG_PUBLISH = 2 };
+//   XCHG_SLICES             XCHG_SUM whose local part is not a sum of per-CTA partials: the CTA that arrives last adds
+//       the `ns` per-slice values of `slices` (p.Ap of every 32-row slice, stored by whichever warp took the slice) in
+//       index order. Saves the grid barrier that would otherwise have to separate sweep A from a fixed per-CTA split
+//       of that sum; deterministic whoever is last. Used when a rank's block is short (several GPUs).
+enum { XCHG_SUM = 0, XCHG_MINMAX = 1, XCHG_PUBLISH = 2, XCHG_SLICES = 3 };
 
 __device__ __forceinline__ void xchg_timeout(const Params& P, unsigned long long t0) {
     if (global_timer_ns() - t0 > 20000000000ull) { // 20 s: a peer is gone
@@ -260,17 +285,20 @@ __device__ __forceinline__ void xchg_timeout(const Params& P, unsigned long long
 
 template <int MODE>
 __device__ __forceinline__ void xchg_all(const Params& P, Xchg& xs, double a, double b, double* part0, double* part1,
-                                         double* sh, int* sflag, double (*xr)[2]) {
+                                         double* sh, int* sflag, double (*xr)[2], const double* slices = nullptr, int ns = 0) {
     constexpr bool MINMAX = MODE == XCHG_MINMAX;
+    constexpr bool SLICES = MODE == XCHG_SLICES;
     const PeerLinks& L = P.L;
     const int W = L.world, nblocks = gridDim.x;
     xs.epoch++;
     xs.count++;
     const unsigned fl = (unsigned) xs.epoch;
-    if (MODE != XCHG_PUBLISH) block_sum2<MINMAX>(a, b, sh);
-    else __syncthreads(); // all halo stores of the CTA precede thread 0's fence
+    if (MODE != XCHG_PUBLISH && !SLICES) block_sum2<MINMAX>(a, b, sh);
+    else __syncthreads(); // all halo stores (per-slice stores) of the CTA precede thread 0's fence
     if (threadIdx.x == 0) {
-        if (MODE != XCHG_PUBLISH) {
+        if (SLICES) {
+            __threadfence();
+        } else if (MODE != XCHG_PUBLISH) {
             part0[blockIdx.x] = a;
             part1[blockIdx.x] = b;
             __threadfence();
@@ -289,7 +317,17 @@ __device__ __forceinline__ void xchg_all(const Params& P, Xchg& xs, double a, do
     if (*sflag) {
         if (MODE != XCHG_PUBLISH) {
             double la = MINMAX ? DBL_MAX : 0.0, lb = MINMAX ? -DBL_MAX : 0.0;
-            for (int i = threadIdx.x; i < nblocks; i += PCG_THREADS) combine2<MINMAX>(la, lb, __ldcg(part0 + i), __ldcg(part1 + i));
+            if (SLICES) {
+                for (int i = threadIdx.x; i < ns; i += 4 * PCG_THREADS) { // four loads in flight, added in index order
+                    double v0 = __ldcg(slices + i), v1 = 0.0, v2 = 0.0, v3 = 0.0;
+                    if (i + PCG_THREADS < ns) v1 = __ldcg(slices + i + PCG_THREADS);
+                    if (i + 2 * PCG_THREADS < ns) v2 = __ldcg(slices + i + 2 * PCG_THREADS);
+                    if (i + 3 * PCG_THREADS < ns) v3 = __ldcg(slices + i + 3 * PCG_THREADS);
+                    la += v0; la += v1; la += v2; la += v3;
+                }
+            } else {
+                for (int i = threadIdx.x; i < nblocks; i += PCG_THREADS) combine2<MINMAX>(la, lb, __ldcg(part0 + i), __ldcg(part1 + i));
+            }
             block_sum2<MINMAX>(la, lb, sh);
             if ((int) threadIdx.x < 2 * W) {
                 const int q = threadIdx.x >> 1, ln = threadIdx.x & 1;
@@ -401,9 +439,25 @@ struct HaloWait {
     int world;
 };
 
+// L2 policy of the matrix stream. The stream of a row block is read once per iteration in full; with the default
+// policy it displaces the five CG vectors (40 B per row) from the L2 on every pass, although they are re-read within
+// the iteration. With `on`, the stream travels as evict_first — the vectors stay L2-resident whenever they fit (sweeps B
+// and C then run from L2, sweep A's p gathers and ap stores hit) — except the first slices [keep_lo, keep_hi), a small
+// share sized by the host (MPSB_L2_RESIDENT_KB, 16 MB) that travels as evict_last and is served from L2 from the second
+// iteration on. Measured on one B200 (profiles/r2_v4_l2_policy_experiment.txt): 48.9 -> 44.5 us/iteration at 0.5 M rows
+// (a rank's block on 8 GPUs), 79.9 -> 73.4 at 1.0 M, 145.0 -> 140.8 at 2.0 M, 269.7 -> 272 at 4.0 M (vectors 160 MB: off
+// there, MPSB_L2_MAX_ROWS). Larger kept shares gain nothing: what the L2 keeps usefully is about 60 MB, not 126 (data
+// read from both dies appears to be held twice); the driver's persisting carve-out changes nothing. Results do not
+// depend on any of this.
+struct L2Plan {
+    int on;
+    int keep_lo, keep_hi;
+    unsigned long long pol_keep, pol_stream;
+};
+
 template <bool C16>
 __device__ __forceinline__ void spmv_sweep(const Params& P, Smem& sm, Pipe& pipe, int sbeg, int nslices, const double* p,
-                                           double* ap, unsigned* ticket, double* slice_pap, const HaloWait& hw) {
+                                           double* ap, unsigned* ticket, double* slice_pap, const HaloWait& hw, const L2Plan& l2) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const size_t K = (size_t) P.K;
     const int nsl_total = nslices - sbeg;
@@ -439,12 +493,22 @@ __device__ __forceinline__ void spmv_sweep(const Params& P, Smem& sm, Pipe& pipe
             sm.meta[warp][st] = StageMeta{slice, nsl, (first ? 1 : 0) | halo, last ? 1 : 0};
             unsigned long long* bar = &sm.full[warp][st];
             mbar_arrive_expect_tx(bar, (first ? 256u : 0u) + (unsigned) nsl * (C16 ? 320u : 384u));
-            if (first) bulk_g2s(S.diag, P.diag + (size_t) slice * 32, 256u, bar);
-            if (nsl > 0) {
-                const size_t off = ((size_t) slice * K + (size_t) pk) * 32;
-bulk_g2s(S.val, P.ell_val + off, (unsigned) nsl * 256u, bar);
-                if (C16) bulk_g2s(S.col, P.ell_col16 + off, (unsigned) nsl * 64u, bar);
-                else bulk_g2s(S.col, P.ell_col + off, (unsigned) nsl * 128u, bar);
+            const size_t off = ((size_t) slice * K + (size_t) pk) * 32;
+            if (l2.on) {
+                const unsigned long long pol = (slice >= l2.keep_lo && slice < l2.keep_hi) ? l2.pol_keep : l2.pol_stream;
+                if (first) bulk_g2s_pol(S.diag, P.diag + (size_t) slice * 32, 256u, bar, pol);
+                if (nsl > 0) {
+                    bulk_g2s_pol(S.val, P.ell_val + off, (unsigned) nsl * 256u, bar, pol);
+                    if (C16) bulk_g2s_pol(S.col, P.ell_col16 + off, (unsigned) nsl * 64u, bar, pol);
+                    else bulk_g2s_pol(S.col, P.ell_col + off, (unsigned) nsl * 128u, bar, pol);
+                }
+            } else {
+                if (first) bulk_g2s(S.diag, P.diag + (size_t) slice * 32, 256u, bar);
+                if (nsl > 0) {
+                    bulk_g2s(S.val, P.ell_val + off, (unsigned) nsl * 256u, bar);
+                    if (C16) bulk_g2s(S.col, P.ell_col16 + off, (unsigned) nsl * 64u, bar);
+                    else bulk_g2s(S.col, P.ell_col + off, (unsigned) nsl * 128u, bar);
+                }
             }
         }
         pipe.issued++;
@@ -675,7 +739,7 @@ __device__ __forceinline__ void spmv_sweep_mf(const Params& P, Smem& sm, Pipe& p
 
 // MULTI = false: one GPU, rows [0, n). MULTI = true: this rank's row block; see the file header.
 template <bool MULTI>
-__global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_blocks, int iteration_cap, int matrix_free) {
+__global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_blocks, int iteration_cap, int matrix_free, int resident_kb) {
     if (*P.cluster_done) { // the cluster solve (k_pcg_cluster.cu) already did it; uniform over the grid
         if (blockIdx.x == 0 && threadIdx.x == 0) *P.ell_wide = 0; // consumed: the next assembly starts from "fits"
         return;
@@ -715,6 +779,22 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     __syncthreads();
     Pipe pipe{0u, 0u};
+
+    // L2 residency plan (see L2Plan): keep the first slices of the block whose stream adds up to the budget. Every CTA
+    // adds the block's slice widths itself (the array is 4 B per 32 rows and L2-resident; once per solve).
+    L2Plan l2{0, 0, 0, 0ull, 0ull};
+    if (resident_kb > 0 && sl_hi > sl_lo) {
+        double w = 0.0, unused = 0.0;
+        for (int sl = sl_lo + (int) threadIdx.x; sl < sl_hi; sl += PCG_THREADS) w += (double) P.ell_width[sl];
+        block_sum2(w, unused, sh);
+        const double bytes = w * (col16 ? 320.0 : 384.0) + 256.0 * (double) (sl_hi - sl_lo);
+        const double share = fmin(1.0, (double) resident_kb * 1024.0 / fmax(bytes, 1.0));
+        l2.on      = 1;
+        l2.keep_lo = sl_lo;
+        l2.keep_hi = sl_lo + (int) (share * (double) (sl_hi - sl_lo));
+        asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(l2.pol_keep));
+        asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(l2.pol_stream));
+    }
 
     // setup: x = 0, r = b, invdiag, p = invdiag r (0 beyond n, up to the slice padding); |b|^2 and r.p
     double l0 = 0.0, l1 = 0.0;
@@ -828,12 +908,17 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
         unsigned* ticket = tickets + (it & 1);
         if (MULTI) hw.epoch = halo_epoch;
         if (col16 && matrix_free) spmv_sweep_mf(P, sm, pipe, sl_lo, sl_hi, p, ap, ticket, P.cg_slice_pap, hw);
-        else if (col16) spmv_sweep<true>(P, sm, pipe, sl_lo, sl_hi, p, ap, ticket, P.cg_slice_pap, hw);
-        else spmv_sweep<false>(P, sm, pipe, sl_lo, sl_hi, p, ap, ticket, P.cg_slice_pap, hw);
+        else if (col16) spmv_sweep<true>(P, sm, pipe, sl_lo, sl_hi, p, ap, ticket, P.cg_slice_pap, hw, l2);
+        else spmv_sweep<false>(P, sm, pipe, sl_lo, sl_hi, p, ap, ticket, P.cg_slice_pap, hw, l2);
         __syncthreads();
         PCG_TICK(0);
         double pap, unused;
-        {
+        if (MULTI && sl_hi - sl_lo <= PCG_SLICE_SUM_MAX) {
+            // short block: the exchange's last CTA adds the per-slice values itself, no grid barrier before it
+            xchg_all<XCHG_SLICES>(P, xs, 0.0, 0.0, part0, part1, sh, &sm.flag, sm.xr, P.cg_slice_pap + sl_lo, sl_hi - sl_lo);
+            xchg_sum2(P, sm.xr, pap, unused);
+            if (tid == 0) tickets[(it + 1) & 1] = 0u; // every CTA of the rank is past sweep A; idle until the next one
+        } else {
             grid.sync();
             // p.ap = sum of the per-slice partials in a fixed order: this CTA's fixed range, then all CTAs
             if (tid == 0) tickets[(it + 1) & 1] = 0u; // the other counter is idle until the next sweep A
@@ -860,12 +945,9 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
 #pragma unroll 2
         for (int j = tid; j < pair_hi - pair_lo; j += stride) {
             const int i = PCG_B_DESC ? pair_hi - 1 - j : pair_lo + j; // see PCG_B_DESC
-            double2 pp = ld2_keep(p, i), rr = ld2_keep(r, i);
+            double2 rr = ld2_keep(r, i);
             double2 aa = ld2_keep(ap, i), dd = reinterpret_cast<const double2*>(invd)[i];
-            double2 xx = reinterpret_cast<const double2*>(x)[i];
-            xx.x += alpha * pp.x; xx.y += alpha * pp.y;
             rr.x -= alpha * aa.x; rr.y -= alpha * aa.y;
-            reinterpret_cast<double2*>(x)[i] = xx;
             st2_keep(r, i, rr);
             lrr += rr.x * rr.x; lrr += rr.y * rr.y;
             lrz += rr.x * (dd.x * rr.x); lrz += rr.y * (dd.y * rr.y);
@@ -873,7 +955,6 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
         if (odd_tail && tid == 0) {
             int i = act_hi - 1;
             double ri = r[i] - alpha * ap[i];
-            x[i] += alpha * p[i];
             r[i] = ri;
             lrr += ri * ri;
             lrz += ri * (invd[i] * ri);
@@ -892,7 +973,16 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
             grid.sync();
             grid_sum2(part1, part2, nblocks, residualNorm2, rz, sh);
         }
-        if (residualNorm2 < threshold) break;
+        if (residualNorm2 < threshold) { // converged: the x update sweep C would have carried (same operands, same rounding)
+            for (int j = tid; j < pair_hi - pair_lo; j += stride) {
+                const int i = pair_lo + j;
+                double2 pp = reinterpret_cast<const double2*>(p)[i], xx = reinterpret_cast<const double2*>(x)[i];
+                xx.x += alpha * pp.x; xx.y += alpha * pp.y;
+                reinterpret_cast<double2*>(x)[i] = xx;
+            }
+            if (odd_tail && tid == 0) x[act_hi - 1] += alpha * p[act_hi - 1];
+            break;
+        }
         const double beta = rz / absNew;
         absNew = rz;
         PCG_TICK(PCG_SPLIT_SYNC ? 1 : 3);
@@ -905,6 +995,9 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
                                 : (PCG_C_DESC ? pair_hi - 1 - j : pair_lo + j);
             double2 pp = ld2_keep(p, i), rr = ld2_keep(r, i);
             double2 dd = reinterpret_cast<const double2*>(invd)[i];
+            double2 xx = reinterpret_cast<const double2*>(x)[i];
+            xx.x += alpha * pp.x; xx.y += alpha * pp.y; // x += alpha p of THIS iteration, carried here so sweep B need not read p
+            reinterpret_cast<double2*>(x)[i] = xx;
             pp.x = dd.x * rr.x + beta * pp.x;
             pp.y = dd.y * rr.y + beta * pp.y;
             st2_keep(p, i, pp);
@@ -915,6 +1008,7 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
         }
         if (odd_tail && tid == 0) {
             int i = act_hi - 1;
+            x[i] += alpha * p[i];
             double v = invd[i] * r[i] + beta * p[i];
             p[i] = v;
             if (MULTI) push_row(i, v);
@@ -967,9 +1061,10 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) spmv_probe_kernel(Params P, in
     unsigned* tickets = reinterpret_cast<unsigned*>(P.cg_partials + 8 * (size_t) max_blocks);
     HaloWait hw{0, 0, sl_hi, nullptr, 0ull, 1};
     const bool col16 = *P.ell_wide == 0;
+    const L2Plan l2{0, 0, 0, 0ull, 0ull};
     if (col16 && matrix_free) spmv_sweep_mf(P, sm, pipe, 0, sl_hi, P.cg_p, P.cg_ap, tickets, P.cg_slice_pap, hw);
-    else if (col16) spmv_sweep<true>(P, sm, pipe, 0, sl_hi, P.cg_p, P.cg_ap, tickets, P.cg_slice_pap, hw);
-    else spmv_sweep<false>(P, sm, pipe, 0, sl_hi, P.cg_p, P.cg_ap, tickets, P.cg_slice_pap, hw);
+    else if (col16) spmv_sweep<true>(P, sm, pipe, 0, sl_hi, P.cg_p, P.cg_ap, tickets, P.cg_slice_pap, hw, l2);
+    else spmv_sweep<false>(P, sm, pipe, 0, sl_hi, P.cg_p, P.cg_ap, tickets, P.cg_slice_pap, hw, l2);
 }
 
 } // namespace
@@ -990,6 +1085,10 @@ int mpsb_pcg_configure(mpsb_handle* h) {
     // matrix-free sweep A: 2-D cases with a flat z (all particles in one plane) only; MPSB_MATRIX_FREE=0/1 overrides
     const mpsb_settings& s = h->P.s;
     const char* mf = getenv("MPSB_MATRIX_FREE");
+    // part of the matrix stream kept L2-resident across iterations (L2Plan): MPSB_L2_RESIDENT_MB, 0 = off
+    const char* l2kb = getenv("MPSB_L2_RESIDENT_KB");
+    h->cg_l2_resident_kb = l2kb ? atoi(l2kb) : MPSB_L2_RESIDENT_KB_DEFAULT;
+    h->cg_l2_max_rows    = getenv("MPSB_L2_MAX_ROWS") ? atoi(getenv("MPSB_L2_MAX_ROWS")) : MPSB_L2_MAX_ROWS_DEFAULT;
     h->cg_matrix_free = (s.dim == 2 && s.domain_max[2] == s.domain_min[2]) ? (mf ? (atoi(mf) ? 1 : 0) : MPSB_MATRIX_FREE_DEFAULT) : 0;
     return 0;
 }
@@ -1006,7 +1105,8 @@ void mpsb_launch_pcg(mpsb_handle* h) {
     if (multi) cudaMemsetAsync(P.L.arrive, 0, 2 * sizeof(unsigned long long), h->stream); // both arrival counters
     int cap = h->cg_iteration_cap;
     int mfree = h->cg_matrix_free;
-    void* args[] = {(void*) &P, (void*) &max_blocks, (void*) &cap, (void*) &mfree};
+    int resident_kb = (P.Np / (multi ? P.L.world : 1) <= h->cg_l2_max_rows) ? h->cg_l2_resident_kb : 0;
+    void* args[] = {(void*) &P, (void*) &max_blocks, (void*) &cap, (void*) &mfree, (void*) &resident_kb};
     const void* fn = multi ? (const void*) pcg_kernel<true> : (const void*) pcg_kernel<false>;
     cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(PCG_THREADS), args, (size_t) h->cg_smem, h->stream);
     h->launches++;

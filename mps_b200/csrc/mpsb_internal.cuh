@@ -201,6 +201,8 @@ struct mpsb_handle {
     int cg_threads;
     int cg_smem;            // dynamic shared memory of the PCG kernel
     int cg_iteration_cap;   // diagnostic: stop the solve after this many iterations (0 = Eigen's 2N)
+    int cg_l2_resident_kb;  // L2 policy of the matrix stream (k_pcg.cu L2Plan): KiB kept with evict_last, the rest evict_first; 0 = off
+    int cg_l2_max_rows;     // ... applied to row blocks of at most this many rows
     int cg_matrix_free;     // sweep A recomputes the off-diagonals from positions instead of streaming them (2-D; MPSB_MATRIX_FREE)
     int num_sms;
     int cl_size, cl_smem;   // cluster solve for small systems (k_pcg_cluster.cu): cluster size (0 = unavailable), dynamic smem
