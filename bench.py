@@ -498,14 +498,19 @@ def run_gpu_arm(args):
         host = {k: pin[k].numpy() for k in pin}
         inputs = {k: host[k] for k in ("type", "position", "velocity")}
         n_e2e = max(1, min(args.steps, args.e2e_steps))
-        h2d = sum(a.nbytes for a in inputs.values())
-        d2h = sum(a.nbytes for a in host.values())
+        # several ranks: each rank moves only ITS block of particle ids over PCIe (mpsb_upload_shard /
+        # mpsb_download_shard); the GPUs all-gather the uploaded blocks over NVLink. Bytes are per rank.
+        shard = world > 1
+        lo, hi = dev.shard_range() if shard else (0, len(t))
+        frac = (hi - lo) / max(1, len(t))
+        h2d = sum(a.nbytes for a in inputs.values()) * frac
+        d2h = sum(a.nbytes for a in host.values()) * frac
         barrier()
         t0 = time.perf_counter()
         for _ in range(n_e2e):
-            dev.upload(inputs)           # H2D of the step's inputs
+            dev.upload(inputs, shard=shard)           # H2D of the step's inputs
             dev.step_forward(False)
-            dev.download_into(host)      # D2H of the step's result (state + pressure) into the same buffers
+            dev.download_into(host, shard=shard)      # D2H of the step's result (state + pressure) into the same buffers
         barrier()
         sec = time.perf_counter() - t0
         if world > 1:
@@ -513,7 +518,9 @@ def run_gpu_arm(args):
             torch.distributed.all_reduce(tt, op=torch.distributed.ReduceOp.MAX)
             sec = float(tt.item())
         e2e = {"value": dev.last_stats.n_active * n_e2e / sec, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
-               "d2h_bytes_per_step": int(d2h), "steps": n_e2e}
+               "d2h_bytes_per_step": int(d2h), "steps": n_e2e,
+               "io": ("sharded by particle id: bytes are PER RANK (1/%d of the state); uploaded blocks are all-gathered "
+                      "between the GPUs over NVLink" % world) if shard else "whole state through one GPU"}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:

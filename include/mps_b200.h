@@ -13,6 +13,9 @@
  *   MPSB_NO_STEP_GRAPH=1         issue the step's launches directly instead of replaying a CUDA graph
  *   MPSB_SMALL_BUILD_MAX_N=<n>   build cell lists in one single-CTA launch up to n particles (default 2048, at most
  *                                32 768; 0 = always the multi-launch radix sort)
+ *   MPSB_NEIGHBOR_TILES=0|1      neighbour build: per-thread walk through L1/L2 (0) or one CTA per 16 cells of a cell row with the
+ *                                3 / 9 neighbouring cell rows staged in shared memory by TMA bulk copies (1); default 0
+ *                                (the tiled build is bit-identical but measured 1.8x slower at 4 M particles)
  *   MPSB_FORCE_WIDE_COLUMNS=1    stream int32 PPE columns even when 16-bit offsets fit
  *   MPSB_CG_ITERATION_CAP=<n>    stop the solve after n iterations (profiling a bounded solve)
  *   MPSB_MATRIX_FREE=0|1         sweep A of the grid solve streams the stored off-diagonals (0) or recomputes them from
@@ -175,6 +178,14 @@ int mpsb_run_phase(mpsb_handle* h, int phase, mpsb_step_stats* stats);
 int mpsb_upload(mpsb_handle* h, uint32_t field_mask, const mpsb_fields* src);
 int mpsb_download(mpsb_handle* h, uint32_t field_mask, const mpsb_fields* dst);
 int64_t mpsb_num_particles(const mpsb_handle* h);
+
+/* Sharded variants for several ranks (both COLLECTIVE): the pointers are still whole arrays indexed by particle id, but rank g
+ * reads / writes only ITS block of ids [first, last) (mpsb_shard_range: [g, g+1) * Np / W clipped to n) — per-rank PCIe
+ * traffic is 1/W of the state. After mpsb_upload_shard the blocks are all-gathered between the GPUs over NVLink, so every
+ * rank's device state is whole, exactly as after mpsb_upload. With one rank they are mpsb_upload / mpsb_download. */
+int mpsb_upload_shard(mpsb_handle* h, uint32_t field_mask, const mpsb_fields* src);
+int mpsb_download_shard(mpsb_handle* h, uint32_t field_mask, const mpsb_fields* dst);
+int mpsb_shard_range(const mpsb_handle* h, int64_t* first, int64_t* last);
 
 /* Page-locked host memory for the buffers passed to mpsb_upload / mpsb_download (cudaHostAlloc: the copies then run
  * as DMA at full PCIe rate with no staging copy inside the driver). Returns NULL on failure; free with mpsb_host_free. */

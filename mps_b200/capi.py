@@ -28,6 +28,7 @@ EXPORTED = [
     "mpsb_upload", "mpsb_download", "mpsb_num_particles", "mpsb_get_neighbors", "mpsb_get_ppe", "mpsb_events",
     "mpsb_comm_unique_id", "mpsb_attach_comm", "mpsb_upload_device", "mpsb_launch_count", "mpsb_set_stream",
     "mpsb_debug_cg_cycles", "mpsb_debug_cg_block_cycles", "mpsb_debug_spmv", "mpsb_host_alloc", "mpsb_host_free",
+    "mpsb_upload_shard", "mpsb_download_shard", "mpsb_shard_range",
 ]
 
 
@@ -103,6 +104,11 @@ def load_library():
     lib.mpsb_comm_unique_id.argtypes = [vp]
     lib.mpsb_attach_comm.restype = i32
     lib.mpsb_attach_comm.argtypes = [vp, i32, i32, vp]
+    for fn in (lib.mpsb_upload_shard, lib.mpsb_download_shard):
+        fn.restype = i32
+        fn.argtypes = [vp, ct.c_uint32, ct.POINTER(CFields)]
+    lib.mpsb_shard_range.restype = i32
+    lib.mpsb_shard_range.argtypes = [vp, ct.POINTER(ct.c_int64), ct.POINTER(ct.c_int64)]
     lib.mpsb_upload_device.restype = i32
     lib.mpsb_upload_device.argtypes = [vp, vp, vp, vp]
     lib.mpsb_set_stream.restype = i32
@@ -218,8 +224,15 @@ class DeviceMPS:
         self._check(self.lib.mpsb_download(self.h, mask, ct.byref(cf)))
         return arrs
 
-    def download_into(self, arrs):
-        """Download into caller-owned (e.g. pinned) contiguous numpy arrays, keyed by field name."""
+    def shard_range(self):
+        """[first, last): the block of particle ids the sharded transfers of this rank move."""
+        lo, hi = ct.c_int64(), ct.c_int64()
+        self._check(self.lib.mpsb_shard_range(self.h, ct.byref(lo), ct.byref(hi)))
+        return int(lo.value), int(hi.value)
+
+    def download_into(self, arrs, shard=False):
+        """Download into caller-owned (e.g. pinned) contiguous numpy arrays, keyed by field name.
+        shard=True (several ranks, collective): only this rank's block of ids is written."""
         cf, mask = CFields(), 0
         for name, dt, w, bit in _FIELD_SPECS:
             a = arrs.get(name)
@@ -229,10 +242,11 @@ class DeviceMPS:
                 raise ValueError(f"download_into: {name} must be C-contiguous {dt.__name__}[{self.n}*{w}]")
             setattr(cf, name, a.ctypes.data)
             mask |= bit
-        self._check(self.lib.mpsb_download(self.h, mask, ct.byref(cf)))
+        self._check((self.lib.mpsb_download_shard if shard else self.lib.mpsb_download)(self.h, mask, ct.byref(cf)))
         return arrs
 
-    def upload(self, arrs):
+    def upload(self, arrs, shard=False):
+        """shard=True (several ranks, collective): only this rank's block of ids crosses PCIe, the GPUs all-gather the rest."""
         cf, mask, keep = CFields(), 0, []
         for name, dt, w, bit in _FIELD_SPECS:
             if name in arrs and arrs[name] is not None:
@@ -240,7 +254,7 @@ class DeviceMPS:
                 keep.append(a)
                 setattr(cf, name, a.ctypes.data)
                 mask |= bit
-        self._check(self.lib.mpsb_upload(self.h, mask, ct.byref(cf)))
+        self._check((self.lib.mpsb_upload_shard if shard else self.lib.mpsb_upload)(self.h, mask, ct.byref(cf)))
 
     def neighbors(self):
         start = np.zeros(self.n + 1, dtype=np.int64)

@@ -234,7 +234,7 @@ int mpsb_create(const mpsb_settings* settings, int64_t n, const int32_t* type, c
     CKC(dalloc(&h->block_hist, (size_t) h->block_hist_cap));
     h->scan_status_cap = h->block_hist_cap / 4096 + 2;
     CKC(dalloc(&h->scan_status, (size_t) h->scan_status_cap + 1)); // [cap] = the ticket counter
-    if (mpsb_pcg_configure(h) != 0) {
+    if (mpsb_neighbors_configure(h) != 0 || mpsb_pcg_configure(h) != 0) {
         snprintf(g_create_error, sizeof g_create_error, "mpsb_create: PCG kernel cannot be made resident");
         mpsb_destroy(h);
         return MPSB_ERR_CUDA;
@@ -250,6 +250,8 @@ int mpsb_create(const mpsb_settings* settings, int64_t n, const int32_t* type, c
         const char* ng = getenv("MPSB_NO_STEP_GRAPH");
         h->graph_enable = ng && atoi(ng) ? 0 : 1;
         h->n_graphs     = 0;
+        const char* nt = getenv("MPSB_NEIGHBOR_TILES");
+        h->neighbor_tiles = nt ? (atoi(nt) ? 1 : 0) : -1;
         const char* nb = getenv("MPSB_SMALL_BUILD_MAX_N");
         h->small_build_max_n = nb ? atoi(nb) : 2048;
         if (h->small_build_max_n > 32768) h->small_build_max_n = 32768;
@@ -352,6 +354,86 @@ int mpsb_download(mpsb_handle* h, uint32_t mask, const mpsb_fields* f) {
     DN(MPSB_F_MIN_PRESSURE, f->minimum_pressure, H.minp, sizeof(double) * N);
     DN(MPSB_F_NUMBER_DENSITY_RATIO, f->number_density_ratio, H.ratio, sizeof(double) * N);
     DN(MPSB_F_BOUNDARY_CONDITION, f->boundary_condition, H.bc, sizeof(int) * N);
+#undef DN
+    CK(h, cudaStreamSynchronize(st));
+    return MPSB_OK;
+}
+
+// ---- sharded state transfer (several ranks): each rank moves only ITS block of particle ids over PCIe ----------
+// Block of rank g: ids [g, g + 1) * Np / W clipped to N (Np = N rounded up to whole 32-row slices x 8, the same split as
+// the row blocks). The array pointers are whole-array pointers indexed by particle id, as in mpsb_upload / mpsb_download;
+// only the block is read / written.
+static void shard_block(const mpsb_handle* h, size_t* lo, size_t* hi) {
+    const size_t N = (size_t) h->P.N, blk = (size_t) (h->P.Np / (h->world > 1 ? h->world : 1));
+    *lo = std::min(N, blk * (size_t) (h->world > 1 ? h->rank : 0));
+    *hi = std::min(N, *lo + blk);
+}
+
+int mpsb_shard_range(const mpsb_handle* h, int64_t* first, int64_t* last) {
+    if (!h || !first || !last) return MPSB_ERR_ARG;
+    size_t lo, hi;
+    shard_block(h, &lo, &hi);
+    *first = (int64_t) lo;
+    *last  = (int64_t) hi;
+    return MPSB_OK;
+}
+
+int mpsb_upload_shard(mpsb_handle* h, uint32_t mask, const mpsb_fields* f) {
+    if (!h || !f) return MPSB_ERR_ARG;
+    if (h->world <= 1) return mpsb_upload(h, mask, f);
+    if (h->sticky) return h->sticky;
+    CK(h, cudaSetDevice(h->device));
+    if (int rc = mpsb_comm_sync_home(h)) return rc; // fields not uploaded keep their latest values
+    size_t lo, hi;
+    shard_block(h, &lo, &hi);
+    const size_t n = hi - lo;
+    Home& H = h->P.H;
+    cudaStream_t st = h->stream;
+    uint32_t present = 0;
+#define UP(bit, dst, src, per, T)                                                                                   \
+    if ((mask & (bit)) && (src)) {                                                                                  \
+        present |= (bit);                                                                                           \
+        if (n) CK(h, cudaMemcpyAsync(dst + lo * (per), src + lo * (per), sizeof(T) * (per) * n, cudaMemcpyHostToDevice, st)); \
+    }
+    UP(MPSB_F_TYPE, H.type, f->type, 1, int);
+    UP(MPSB_F_POSITION, H.pos, f->position, 3, double);
+    UP(MPSB_F_VELOCITY, H.vel, f->velocity, 3, double);
+    UP(MPSB_F_ACCEL, H.acc, f->acceleration, 3, double);
+    UP(MPSB_F_PRESSURE, H.p, f->pressure, 1, double);
+    UP(MPSB_F_MIN_PRESSURE, H.minp, f->minimum_pressure, 1, double);
+    UP(MPSB_F_NUMBER_DENSITY_RATIO, H.ratio, f->number_density_ratio, 1, double);
+    UP(MPSB_F_BOUNDARY_CONDITION, H.bc, f->boundary_condition, 1, int);
+#undef UP
+    if (int rc = mpsb_comm_allgather_home(h, present)) return rc; // the other ranks' blocks arrive over NVLink
+    const size_t N = (size_t) h->P.N;
+    if ((present & (MPSB_F_NUMBER_DENSITY_RATIO | MPSB_F_TYPE)) && N > 0) mpsb_launch_ghost_ratio_from_home(h);
+    if (h->have_lists && N > 0) mpsb_launch_gather_all(h);
+    h->home_current = true;
+    CK(h, cudaStreamSynchronize(st));
+    return MPSB_OK;
+}
+
+int mpsb_download_shard(mpsb_handle* h, uint32_t mask, const mpsb_fields* f) {
+    if (!h || !f) return MPSB_ERR_ARG;
+    if (h->world <= 1) return mpsb_download(h, mask, f);
+    if (h->sticky) return h->sticky;
+    CK(h, cudaSetDevice(h->device));
+    if (int rc = mpsb_comm_sync_home(h)) return rc;
+    size_t lo, hi;
+    shard_block(h, &lo, &hi);
+    const size_t n = hi - lo;
+    Home& H = h->P.H;
+    cudaStream_t st = h->stream;
+#define DN(bit, dst, src, per, T)                                                                                   \
+    if ((mask & (bit)) && (dst) && n) CK(h, cudaMemcpyAsync(dst + lo * (per), src + lo * (per), sizeof(T) * (per) * n, cudaMemcpyDeviceToHost, st))
+    DN(MPSB_F_TYPE, f->type, H.type, 1, int);
+    DN(MPSB_F_POSITION, f->position, H.pos, 3, double);
+    DN(MPSB_F_VELOCITY, f->velocity, H.vel, 3, double);
+    DN(MPSB_F_ACCEL, f->acceleration, H.acc, 3, double);
+    DN(MPSB_F_PRESSURE, f->pressure, H.p, 1, double);
+    DN(MPSB_F_MIN_PRESSURE, f->minimum_pressure, H.minp, 1, double);
+    DN(MPSB_F_NUMBER_DENSITY_RATIO, f->number_density_ratio, H.ratio, 1, double);
+    DN(MPSB_F_BOUNDARY_CONDITION, f->boundary_condition, H.bc, 1, int);
 #undef DN
     CK(h, cudaStreamSynchronize(st));
     return MPSB_OK;

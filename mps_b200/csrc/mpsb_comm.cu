@@ -202,6 +202,26 @@ int mpsb_comm_sync_home(mpsb_handle* h) {
     return MPSB_OK;
 }
 
+// Sharded upload (mpsb_upload_shard): every rank copied its block of particle ids into its HOME arrays; all-gather
+// the blocks of the uploaded fields over NVLink so that HOME is whole on every rank again.
+int mpsb_comm_allgather_home(mpsb_handle* h, uint32_t mask) {
+    if (h->world <= 1) return MPSB_OK;
+    Home& H = h->P.H;
+#define GA(bit, ptr, per)                                                                          \
+    if (mask & (bit))                                                                              \
+        if (int rc = gather_rows(h, ptr, per, "ncclAllGather(home)")) return rc
+    GA(MPSB_F_TYPE, H.type, 1);
+    GA(MPSB_F_POSITION, H.pos, 3);
+    GA(MPSB_F_VELOCITY, H.vel, 3);
+    GA(MPSB_F_ACCEL, H.acc, 3);
+    GA(MPSB_F_PRESSURE, H.p, 1);
+    GA(MPSB_F_MIN_PRESSURE, H.minp, 1);
+    GA(MPSB_F_NUMBER_DENSITY_RATIO, H.ratio, 1);
+    GA(MPSB_F_BOUNDARY_CONDITION, H.bc, 1);
+#undef GA
+    return MPSB_OK;
+}
+
 // Counters of the step: every rank counted its own rows; all-gather the structs and combine (k_halo.cu).
 void mpsb_launch_combine_stats(mpsb_handle* h);
 int mpsb_comm_combine_stats(mpsb_handle* h) {

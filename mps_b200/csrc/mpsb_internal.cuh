@@ -208,6 +208,7 @@ struct mpsb_handle {
     int cl_size, cl_smem;   // cluster solve for small systems (k_pcg_cluster.cu): cluster size (0 = unavailable), dynamic smem
     int cl_launched;        // the cluster kernel has run on this handle (*cluster_done may be set)
     int cl_disable;         // MPSB_NO_CLUSTER_SOLVE=1: always use the grid kernel (tests)
+    int neighbor_tiles;     // MPSB_NEIGHBOR_TILES: 1 / 0 force the tiled (TMA-staged) / per-thread neighbour build, -1 = default (per-thread)
     int small_build_max_n;  // single-launch cell build up to this many particles (MPSB_SMALL_BUILD_MAX_N; 0 = never)
     int in_step;            // inside mpsb_step: DevStats was cleared as a whole, launchers skip their own clears
     int graph_enable;       // small cases: replay the step as one CUDA graph (MPSB_NO_STEP_GRAPH=1 disables)
@@ -232,6 +233,7 @@ void mpsb_launch_cell_build(mpsb_handle* h, bool scatter_first); // k_cells.cu: 
 void mpsb_launch_gather_all(mpsb_handle* h);            // HOME -> SORTED with the current perm
 void mpsb_launch_scatter_all(mpsb_handle* h);           // SORTED -> HOME
 void mpsb_launch_neighbors(mpsb_handle* h);             // k_neighbors.cu
+int mpsb_neighbors_configure(mpsb_handle* h);           // shared-memory opt-in of the tiled build
 void mpsb_launch_number_density(mpsb_handle* h);
 void mpsb_launch_ghost_ratio_from_home(mpsb_handle* h); // after an upload: a Ghost's recorded sum is its uploaded ratio
 void mpsb_launch_explicit(mpsb_handle* h);              // k_explicit.cu
@@ -251,6 +253,7 @@ void mpsb_comm_release(mpsb_handle* h);
 // ---- slab decomposition (world > 1) ----
 int mpsb_comm_allgather_keyrow(mpsb_handle* h);         // mpsb_comm.cu: NCCL all-gather of the own-block cell keys
 int mpsb_comm_sync_home(mpsb_handle* h);                // all-gather every SORTED field, then SORTED -> HOME for all rows
+int mpsb_comm_allgather_home(mpsb_handle* h, uint32_t field_mask); // id blocks of the HOME fields in the mask -> whole arrays on every rank
 int mpsb_comm_combine_stats(mpsb_handle* h);            // all-gather DevStats, combine into *P.stats
 int mpsb_comm_allreduce_dflags(mpsb_handle* h, int* host2); // Dirichlet fixpoint: OR of the two flags over the ranks
 void mpsb_launch_xbarrier(mpsb_handle* h);              // k_halo.cu: cross-rank barrier on the stream (epoch flags in the inboxes)

@@ -99,19 +99,30 @@ def main():
     for name in free:
         scale = max(float(np.abs(b[name]).max()), 1e-300)
         free[name] = float(np.abs(a[name] - b[name]).max()) / scale
+    # (3) sharded transfers: a rank's mpsb_download_shard writes exactly its block of ids (and the right values);
+    # after mpsb_upload_shard of the single-GPU state the device state is whole on every rank
+    lo, hi = multi.shard_range()
+    part = {k: np.full_like(a[k], 7) for k in ("type", "position", "velocity", "pressure")}
+    multi.download_into(part, shard=True)
+    shard_ok = all(np.array_equal(part[k][lo:hi], a[k][lo:hi]) and (part[k][:lo] == 7).all() and (part[k][hi:] == 7).all()
+                   for k in part)
+    multi.upload({k: b[k] for k in ("type", "position", "velocity", "pressure")}, shard=True)
+    a2 = multi.download(["type", "position", "velocity", "pressure"])
+    shard_ok &= all(np.array_equal(a2[k], b[k]) for k in a2)
+    multi.upload({k: a[k] for k in ("type", "position", "velocity", "pressure")})
     # every rank must hold the same bits
     mine = torch.from_numpy(np.concatenate([a["pressure"], a["velocity"].ravel(), a["position"].ravel()])).cuda()
     ref = mine.clone()
     dist.broadcast(ref, src=0)
     same = torch.tensor([int(torch.equal(mine.view(torch.int64), ref.view(torch.int64)))], device="cuda")
     dist.all_reduce(same, op=dist.ReduceOp.MIN)
-    ok = bool(same.item()) and flags_equal and counters_equal and all(x <= 1e-10 for x in worst.values()) and \
+    ok = bool(same.item()) and flags_equal and counters_equal and shard_ok and all(x <= 1e-10 for x in worst.values()) and \
         all(x <= 1e-8 for x in free.values()) and (vs_reference is None or vs_reference["ok"])
     okt = torch.tensor([int(ok)], device="cuda")
     dist.all_reduce(okt, op=dist.ReduceOp.MIN)
     if rank == 0:
         print(json.dumps({"case": what, "world": world, "steps": steps, "ranks_bit_identical": bool(same.item()),
-                          "flags_equal": flags_equal, "counters_equal": counters_equal, "max_rel_diff_vs_single_gpu": worst,
+                          "flags_equal": flags_equal, "counters_equal": counters_equal, "sharded_transfers_ok": bool(shard_ok), "max_rel_diff_vs_single_gpu": worst,
                           "free_run_3_steps_max_rel_diff": free, "vs_compiled_reference": vs_reference,
                           "collisions_replayed": collisions, "particles_ghosted": ghosted,
                           "cg_iterations_multi_vs_single": iters[-3:], "ok": bool(okt.item())}), flush=True)
