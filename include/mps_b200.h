@@ -20,6 +20,9 @@
  *   MPSB_CG_ITERATION_CAP=<n>    stop the solve after n iterations (profiling a bounded solve)
  *   MPSB_MATRIX_FREE=0|1         sweep A of the grid solve streams the stored off-diagonals (0) or recomputes them from
  *                                positions (1; 2-D cases only)
+ *   MPSB_CG_SINGLE_REDUCTION=1   grid solve with the Chronopoulos-Gear recurrence: one global reduction and two grid-wide
+ *                                synchronisations per iteration instead of two and four; same Krylov space and stopping rule,
+ *                                different rounding (held to 1e-10 / +-2 % iterations, not bit-identical); never the default
  *   MPSB_L2_RESIDENT_KB=<kb>     L2 policy of the solve's matrix stream: <kb> KiB travel as evict_last, the rest as evict_first
  *                                (default 16384; 0 = no policy), for row blocks of at most MPSB_L2_MAX_ROWS rows (2 500 000)
  * and by the host mirror (mps_b200/host): MPSB_DEVICE=<ordinal>, MPSB_CSV_FLOAT=gcc5.
@@ -105,6 +108,7 @@ typedef struct mpsb_step_stats {
     int32_t ppe_columns_16bit;   /* 1: the solve streamed 16-bit column offsets (10 B per entry), 0: int32 columns (12 B) */
     int32_t solve_in_cluster;    /* 1: the small-system cluster kernel did the solve (k_pcg_cluster.cu), 0: the grid kernel */
     int32_t ppe_matrix_free;     /* 1: sweep A of the solve recomputed the off-diagonals from positions (2 B per entry streamed) */
+    int32_t cg_single_reduction; /* 1: the solve ran the single-reduction (Chronopoulos-Gear) recurrence (MPSB_CG_SINGLE_REDUCTION=1) */
 } mpsb_step_stats;
 
 typedef struct mpsb_handle mpsb_handle;

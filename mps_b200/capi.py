@@ -40,7 +40,7 @@ class CStepStats(ct.Structure):
         ("cg_iterations", ct.c_int32), ("n_active", ct.c_int32), ("n_inner", ct.c_int32), ("n_surface", ct.c_int32),
         ("nnz", ct.c_int32), ("n_ghosted", ct.c_int32), ("n_unconnected", ct.c_int32), ("n_collisions", ct.c_int32),
         ("max_neighbors", ct.c_int32), ("courant_exceeds_cfl", ct.c_int32), ("ppe_columns_16bit", ct.c_int32), ("solve_in_cluster", ct.c_int32),
-        ("ppe_matrix_free", ct.c_int32),
+        ("ppe_matrix_free", ct.c_int32), ("cg_single_reduction", ct.c_int32),
     ]
 
     def as_dict(self):

@@ -110,6 +110,7 @@ struct Smem {
     double red[66];
     int need[MPSB_MAX_RANKS][2]; // MULTI: my rows each peer reads, [lo, hi)
     double xr[MPSB_MAX_RANKS][2]; // MULTI: every rank's pair of the last exchange
+    double xr3[MPSB_MAX_RANKS][3]; // MULTI, single-reduction recurrence: every rank's triple
     int flag;                    // MULTI: this CTA arrived last at the running exchange
 };
 
@@ -318,12 +319,14 @@ __device__ __forceinline__ void xchg_all(const Params& P, Xchg& xs, double a, do
         if (MODE != XCHG_PUBLISH) {
             double la = MINMAX ? DBL_MAX : 0.0, lb = MINMAX ? -DBL_MAX : 0.0;
             if (SLICES) {
-                for (int i = threadIdx.x; i < ns; i += 4 * PCG_THREADS) { // four loads in flight, added in index order
-                    double v0 = __ldcg(slices + i), v1 = 0.0, v2 = 0.0, v3 = 0.0;
-                    if (i + PCG_THREADS < ns) v1 = __ldcg(slices + i + PCG_THREADS);
-                    if (i + 2 * PCG_THREADS < ns) v2 = __ldcg(slices + i + 2 * PCG_THREADS);
-                    if (i + 3 * PCG_THREADS < ns) v3 = __ldcg(slices + i + 3 * PCG_THREADS);
-                    la += v0; la += v1; la += v2; la += v3;
+                // sixteen loads in flight per thread (a block of 31 k slices is 49 per thread: four L2 round trips, not
+                // twelve), added in index order
+                for (int i = threadIdx.x; i < ns; i += 16 * PCG_THREADS) {
+                    double v[16];
+#pragma unroll
+                    for (int k = 0; k < 16; k++) v[k] = (i + k * PCG_THREADS < ns) ? __ldcg(slices + i + k * PCG_THREADS) : 0.0;
+#pragma unroll
+                    for (int k = 0; k < 16; k++) la += v[k];
                 }
             } else {
                 for (int i = threadIdx.x; i < nblocks; i += PCG_THREADS) combine2<MINMAX>(la, lb, __ldcg(part0 + i), __ldcg(part1 + i));
@@ -363,6 +366,67 @@ __device__ __forceinline__ void xchg_all(const Params& P, Xchg& xs, double a, do
     }
     __syncthreads();
 }
+// Three sums in ONE exchange (single-reduction recurrence, MPSB_CG_SINGLE_REDUCTION): (a, b) from per-CTA partials and c
+// from the `ns` per-slice values of `slices`, both added by the CTA that arrives last, in index order. Wire format as
+// XCHG_SUM, three 16-byte lines per rank, in a second region of the inbox (1 KiB behind the pairs). Result: xr3[q][0..2].
+__device__ __forceinline__ void xchg_sum3(const Params& P, Xchg& xs, double a, double b, double* part0, double* part1, double* sh, int* sflag,
+                                          double (*xr3)[3], const double* slices, int ns) {
+    const PeerLinks& L = P.L;
+    const int W = L.world, nblocks = gridDim.x;
+    xs.epoch++;
+    xs.count++;
+    const unsigned fl = (unsigned) xs.epoch;
+    block_sum2(a, b, sh);
+    if (threadIdx.x == 0) {
+        part0[blockIdx.x] = a;
+        part1[blockIdx.x] = b;
+        __threadfence();
+        unsigned long long t = atomicAdd(L.arrive, 1ull);
+        const int last = (t + 1ull == xs.count * (unsigned long long) nblocks) ? 1 : 0;
+        if (last) __threadfence();
+        *sflag = last;
+    }
+    __syncthreads();
+    if (*sflag) {
+        double la = 0.0, lb = 0.0, lc = 0.0, zero = 0.0;
+        for (int i = threadIdx.x; i < nblocks; i += PCG_THREADS) {
+            la += __ldcg(part0 + i);
+            lb += __ldcg(part1 + i);
+        }
+        for (int i = threadIdx.x; i < ns; i += 16 * PCG_THREADS) {
+            double v[16];
+#pragma unroll
+            for (int k = 0; k < 16; k++) v[k] = (i + k * PCG_THREADS < ns) ? __ldcg(slices + i + k * PCG_THREADS) : 0.0;
+#pragma unroll
+            for (int k = 0; k < 16; k++) lc += v[k];
+        }
+        block_sum2(la, lb, sh);
+        block_sum2(lc, zero, sh);
+        if ((int) threadIdx.x < 3 * W) {
+            const int q = threadIdx.x / 3, ln = threadIdx.x - 3 * q;
+            const double v = ln == 0 ? la : (ln == 1 ? lb : lc);
+            double* dst = L.peer_red[q] + 128 + ((size_t) (xs.epoch & 1ull) * MPSB_MAX_RANKS + L.rank) * 6 + ln * 2;
+            asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %2};" ::"l"(dst), "r"((unsigned) __double2loint(v)), "r"(fl),
+                         "r"((unsigned) __double2hiint(v))
+                         : "memory");
+        }
+    }
+    if ((int) threadIdx.x < 3 * W) {
+        const int q = threadIdx.x / 3, ln = threadIdx.x - 3 * q;
+        const double* src = L.red + 128 + ((size_t) (xs.epoch & 1ull) * MPSB_MAX_RANKS + q) * 6 + ln * 2;
+        const unsigned long long t0 = global_timer_ns();
+        unsigned x, f0, y, f1, spins = 0;
+        for (;;) {
+            asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(x), "=r"(f0), "=r"(y), "=r"(f1) : "l"(src) : "memory");
+            if (f0 == fl && f1 == fl) break;
+            if ((++spins & 1023u) == 0) xchg_timeout(P, t0);
+        }
+        xr3[q][ln] = __hiloint2double((int) y, (int) x);
+        __threadfence();
+    }
+    __syncthreads();
+}
+
 // sum over ranks in rank order: bit-identical on every rank
 __device__ __forceinline__ void xchg_sum2(const Params& P, double (*xr)[2], double& a, double& b) {
     a = 0.0;
@@ -738,7 +802,7 @@ __device__ __forceinline__ void spmv_sweep_mf(const Params& P, Smem& sm, Pipe& p
 }
 
 // MULTI = false: one GPU, rows [0, n). MULTI = true: this rank's row block; see the file header.
-template <bool MULTI>
+template <bool MULTI, bool SR>
 __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_blocks, int iteration_cap, int matrix_free, int resident_kb) {
     if (*P.cluster_done) { // the cluster solve (k_pcg_cluster.cu) already did it; uniform over the grid
         if (blockIdx.x == 0 && threadIdx.x == 0) *P.ell_wide = 0; // consumed: the next assembly starts from "fits"
@@ -903,6 +967,125 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
     const int high_pairs = MULTI ? max(0, min(pair_hi - pair_lo, pair_hi - (max(push_gap_hi, row_lo) >> 1))) : 0;
     long long cyc[4] = {0, 0, 0, 0}, t0 = clock64(), t1;
 #define PCG_TICK(slot) do { t1 = clock64(); cyc[slot] += t1 - t0; t0 = t1; } while (0)
+    if (SR) {
+        // ---- single-reduction recurrence (Chronopoulos & Gear 1989), MPSB_CG_SINGLE_REDUCTION=1, never the default ----
+        // Same Krylov space, same stopping rule on the recursively updated |r|^2, but ONE global reduction per
+        // iteration instead of two (and two grid-wide synchronisations instead of four): with u = D^-1 r, w = A u,
+        //     gamma = r.u, delta = u.w, |r|^2            one reduction, after the sweep that forms w
+        //     beta = gamma / gamma_old, alpha = gamma / (delta - beta gamma / alpha_old)
+        //     d = u + beta d; s = w + beta s; x += alpha d; r -= alpha s; u = D^-1 r        one fused vector sweep
+        // (d is the search direction p of the textbook loop, s = A d by recurrence instead of by product). The
+        // scalars differ from Eigen's in rounding (delta - beta gamma / alpha against p.Ap), so this mode is held to
+        // the 1e-10 / +-2 % bars, not to bit-identity with the default loop. The convergence test of update k arrives
+        // with the reduction of sweep k + 1: one product is spent after convergence. u lives in cg_p (the vector sweep A
+        // gathers and the one whose halo rows travel), w in cg_ap.
+        double* u = p;
+        double* w = ap;
+        double* d = P.cg_dir;
+        double* s = P.cg_s;
+        double gamma = absNew, alpha = 0.0, lg = 0.0, lrr = 0.0;
+        bool first = true;
+        unsigned sweeps = 0; // sweep A count: the slice queue alternates per SWEEP (`it` lags one sweep behind here)
+        while (!done) {
+            unsigned* ticket = tickets + (sweeps & 1u);
+            if (MULTI) hw.epoch = halo_epoch;
+            if (col16) spmv_sweep<true>(P, sm, pipe, sl_lo, sl_hi, u, w, ticket, P.cg_slice_pap, hw, l2);
+            else spmv_sweep<false>(P, sm, pipe, sl_lo, sl_hi, u, w, ticket, P.cg_slice_pap, hw, l2);
+            __syncthreads();
+            PCG_TICK(0);
+            double G, RR, D;
+            if (MULTI) {
+                xchg_sum3(P, xs, lg, lrr, part0, part1, sh, &sm.flag, sm.xr3, P.cg_slice_pap + sl_lo, sl_hi - sl_lo);
+                G = RR = D = 0.0;
+                for (int q = 0; q < W; q++) {
+                    G += sm.xr3[q][0];
+                    RR += sm.xr3[q][1];
+                    D += sm.xr3[q][2];
+                }
+                if (tid == 0) tickets[(sweeps + 1u) & 1u] = 0u;
+            } else {
+                grid.sync(); // every slice of the sweep has its u.w stored
+                if (tid == 0) tickets[(sweeps + 1u) & 1u] = 0u;
+                double ld = 0.0, zero = 0.0;
+                {
+                    const int nsl = sl_hi - sl_lo, per = (nsl + nblocks - 1) / nblocks;
+                    const int lo = sl_lo + blockIdx.x * per, hi = min(lo + per, sl_hi);
+                    for (int i = lo + (int) threadIdx.x; i < hi; i += PCG_THREADS) ld += __ldcg(P.cg_slice_pap + i);
+                }
+                block_sum2(lg, lrr, sh);
+                block_sum2(ld, zero, sh);
+                if (threadIdx.x == 0) {
+                    part0[blockIdx.x] = lg;
+                    part1[blockIdx.x] = lrr;
+                    part2[blockIdx.x] = ld;
+                }
+                grid.sync();
+                grid_sum2(part0, part1, nblocks, G, RR, sh);
+                grid_sum2(part2, part2, nblocks, D, zero, sh); // (the partials are rewritten two grid barriers from here)
+            }
+            sweeps++;
+            double beta = 0.0;
+            if (first) {
+                alpha = gamma / D;
+            } else {
+                residualNorm2 = RR;
+                if (RR < threshold) break;
+                it++;
+                if (it >= maxIters) break;
+                beta  = G / gamma;
+                alpha = G / (D - beta * G / alpha);
+                gamma = G;
+            }
+            PCG_TICK(3);
+            // ---- fused vector sweep: d, s, x, r, u; partials of r.u and |r|^2 ----
+            lg = 0.0;
+            lrr = 0.0;
+            for (int j = tid; j < pair_hi - pair_lo; j += stride) {
+                const int i = MULTI ? (j < high_pairs ? pair_hi - high_pairs + j : pair_lo + j - high_pairs) : pair_lo + j;
+                double2 uu = reinterpret_cast<const double2*>(u)[i], ww = reinterpret_cast<const double2*>(w)[i];
+                double2 dd = uu, ss = ww;
+                if (!first) {
+                    const double2 d0 = reinterpret_cast<const double2*>(d)[i], s0 = reinterpret_cast<const double2*>(s)[i];
+                    dd.x = uu.x + beta * d0.x; dd.y = uu.y + beta * d0.y;
+                    ss.x = ww.x + beta * s0.x; ss.y = ww.y + beta * s0.y;
+                }
+                double2 xx = reinterpret_cast<const double2*>(x)[i], rr = reinterpret_cast<const double2*>(r)[i];
+                const double2 id = reinterpret_cast<const double2*>(invd)[i];
+                xx.x += alpha * dd.x; xx.y += alpha * dd.y;
+                rr.x -= alpha * ss.x; rr.y -= alpha * ss.y;
+                uu.x = id.x * rr.x; uu.y = id.y * rr.y;
+                reinterpret_cast<double2*>(d)[i] = dd;
+                reinterpret_cast<double2*>(s)[i] = ss;
+                reinterpret_cast<double2*>(x)[i] = xx;
+                reinterpret_cast<double2*>(r)[i] = rr;
+                reinterpret_cast<double2*>(u)[i] = uu;
+                lg += rr.x * uu.x; lg += rr.y * uu.y;
+                lrr += rr.x * rr.x; lrr += rr.y * rr.y;
+                if (MULTI) {
+                    push_row(2 * i, uu.x);
+                    push_row(2 * i + 1, uu.y);
+                }
+            }
+            if (odd_tail && tid == 0) {
+                const int i = act_hi - 1;
+                const double di = first ? u[i] : u[i] + beta * d[i], si = first ? w[i] : w[i] + beta * s[i];
+                const double ri = r[i] - alpha * si, ui = invd[i] * ri;
+                x[i] += alpha * di;
+                d[i] = di; s[i] = si; r[i] = ri; u[i] = ui;
+                lg += ri * ui;
+                lrr += ri * ri;
+                if (MULTI) push_row(i, ui);
+            }
+            first = false;
+            PCG_TICK(1);
+            if (MULTI) {
+                publish_split(P, xs, publishes, did_push);
+                did_push   = false;
+                halo_epoch = xs.epoch;
+            } else grid.sync();
+            PCG_TICK(3);
+        }
+    } else
     while (!done && it < maxIters) {
         // ---- sweep A: ap = A p, p.ap ----
         unsigned* ticket = tickets + (it & 1);
@@ -1033,7 +1216,7 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) pcg_kernel(Params P, int max_b
         for (int k = 0; k < 4; k++) P.stats->cg_cycles[k] = cyc[k];
         P.stats->cg_iterations   = it;
         P.stats->pad[0]          = col16 ? 1 : 0;
-        P.stats->pad[1]          = (col16 && matrix_free) ? 2 : 0; // bit 1: sweep A recomputed the off-diagonals
+        P.stats->pad[1]          = ((col16 && matrix_free) ? 2 : 0) | (SR ? 4 : 0); // bit 1: sweep A recomputed the off-diagonals; bit 2: single-reduction recurrence
         // leave the launch-scoped scratch cleared for the next solve (saves memset nodes): the two slice-queue
         // counters (no sweep A is running any more) and the column-width flag of the assembly just consumed
         tickets[0] = 0u;
@@ -1071,11 +1254,16 @@ __global__ void __launch_bounds__(PCG_THREADS, 1) spmv_probe_kernel(Params P, in
 
 int mpsb_pcg_configure(mpsb_handle* h) {
     int smem = (int) sizeof(Smem);
-    if (cudaFuncSetAttribute(pcg_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return -1;
-    if (cudaFuncSetAttribute(pcg_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return -1;
+    if (cudaFuncSetAttribute(pcg_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return -1;
+    if (cudaFuncSetAttribute(pcg_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return -1;
+    if (cudaFuncSetAttribute(pcg_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return -1;
+    if (cudaFuncSetAttribute(pcg_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return -1;
+    // opt-in: one global reduction per iteration (Chronopoulos-Gear recurrence); different rounding, never the default
+    const char* sr = getenv("MPSB_CG_SINGLE_REDUCTION");
+    h->cg_single_reduction = sr && atoi(sr) ? 1 : 0;
     if (cudaFuncSetAttribute(spmv_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return -1;
     int per_sm = 0;
-    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, pcg_kernel<true>, PCG_THREADS, smem);
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, pcg_kernel<true, true>, PCG_THREADS, smem);
     if (e != cudaSuccess || per_sm < 1) return -1;
     h->cg_threads    = PCG_THREADS;
     h->cg_smem       = smem;
@@ -1107,7 +1295,9 @@ void mpsb_launch_pcg(mpsb_handle* h) {
     int mfree = h->cg_matrix_free;
     int resident_kb = (P.Np / (multi ? P.L.world : 1) <= h->cg_l2_max_rows) ? h->cg_l2_resident_kb : 0;
     void* args[] = {(void*) &P, (void*) &max_blocks, (void*) &cap, (void*) &mfree, (void*) &resident_kb};
-    const void* fn = multi ? (const void*) pcg_kernel<true> : (const void*) pcg_kernel<false>;
+    const bool sr = h->cg_single_reduction && !mfree;
+    const void* fn = multi ? (sr ? (const void*) pcg_kernel<true, true> : (const void*) pcg_kernel<true, false>)
+                           : (sr ? (const void*) pcg_kernel<false, true> : (const void*) pcg_kernel<false, false>);
     cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(PCG_THREADS), args, (size_t) h->cg_smem, h->stream);
     h->launches++;
 }

@@ -110,6 +110,7 @@ void fill_stats(mpsb_handle* h, mpsb_step_stats* st) {
     st->ppe_columns_16bit = d.pad[0];
     st->solve_in_cluster  = d.pad[1] & 1;
     st->ppe_matrix_free   = (d.pad[1] >> 1) & 1;
+    st->cg_single_reduction = (d.pad[1] >> 2) & 1;
     st->courant_exceeds_cfl = d.courant_bits_as_double > h->P.s.cfl_condition;
 }
 
@@ -241,6 +242,7 @@ int mpsb_create(const mpsb_settings* settings, int64_t n, const int32_t* type, c
     }
     CKC(dalloc(&P.cg_partials, 8 * (size_t) h->cg_max_blocks + 8));
     CKC(dalloc(&P.cg_slice_pap, N / 32 + 1));
+    if (h->cg_single_reduction) { CKC(dalloc(&P.cg_dir, N)); CKC(dalloc(&P.cg_s, N)); }
     CKC(dalloc(&P.cluster_done, 1));
     CKC(dalloc(&P.row_xy, N));
     mpsb_pcg_cluster_configure(h); // optional fast path for small systems; 0 = this device cannot co-schedule a cluster
@@ -282,7 +284,7 @@ int mpsb_destroy(mpsb_handle* h) {
     void* ptrs[] = {S.x, S.y, S.z, S.u, S.v, S.w, S.u2, S.v2, S.w2, S.ax, S.ay, S.az, S.minp, S.ratio, S.type,
                     S.id, h->arena, H.inv, H.inv_alt, P.keyrow, P.ext, P.dflags, P.cstate, P.stats_all, P.key, P.key_alt,
                     P.val, P.val_alt, P.cell_start, P.cell_end, P.nbr_count, P.nbr_idx, P.nbr_dist, P.ell_count,
-                    P.ell_width, P.ell_cmin, P.ell_cmax, P.ell_col, P.ell_col16, P.ell_wide, P.ell_val, P.diag, P.rhs, P.cg_r, P.cg_p, P.cg_ap, P.cg_invdiag, P.cg_partials, P.cg_slice_pap, P.cluster_done, P.row_xy,
+                    P.ell_width, P.ell_cmin, P.ell_cmax, P.ell_col, P.ell_col16, P.ell_wide, P.ell_val, P.diag, P.rhs, P.cg_r, P.cg_p, P.cg_ap, P.cg_invdiag, P.cg_partials, P.cg_slice_pap, P.cg_dir, P.cg_s, P.cluster_done, P.row_xy,
                     P.parent, P.mark, P.cand, P.cand_count, P.ev_ghost_id, P.ev_ghost_xyz, P.ev_uncon_id, P.stats,
                     h->block_hist, h->scan_status};
     for (void* p : ptrs)

@@ -130,6 +130,7 @@ struct Params {
     double *diag, *rhs;        // N
     double *cg_r, *cg_p, *cg_ap, *cg_invdiag; // N
     double *cg_partials;       // 8 * max_blocks + 1: 3 reduction rows, 5 diagnostic rows, 2 slice-queue counters
+    double *cg_dir, *cg_s;     // N each: search direction and s = A d of the single-reduction recurrence (MPSB_CG_SINGLE_REDUCTION)
     double *cg_slice_pap;      // Np/32 + 1: p.Ap of each 32-row slice (deterministic two-level sum)
     double2 *row_xy;           // Np: (x, y) of every SORTED row as one 16-byte record, written by the assembly for the
                                // matrix-free sweep A (k_pcg.cu): off-diagonals are recomputed from positions
@@ -203,6 +204,7 @@ struct mpsb_handle {
     int cg_iteration_cap;   // diagnostic: stop the solve after this many iterations (0 = Eigen's 2N)
     int cg_l2_resident_kb;  // L2 policy of the matrix stream (k_pcg.cu L2Plan): KiB kept with evict_last, the rest evict_first; 0 = off
     int cg_l2_max_rows;     // ... applied to row blocks of at most this many rows
+    int cg_single_reduction; // MPSB_CG_SINGLE_REDUCTION=1: Chronopoulos-Gear recurrence in the grid solve (one reduction per iteration)
     int cg_matrix_free;     // sweep A recomputes the off-diagonals from positions instead of streaming them (2-D; MPSB_MATRIX_FREE)
     int num_sms;
     int cl_size, cl_smem;   // cluster solve for small systems (k_pcg_cluster.cu): cluster size (0 = unavailable), dynamic smem

@@ -472,7 +472,7 @@ def test_full_size_case_properties():
 
 
 @pytest.mark.parametrize("path", U.large_golden_files(), ids=lambda p: p.split("/")[-1][:-4])
-@pytest.mark.parametrize("columns", ["col16", "col32", "matrix_free"])
+@pytest.mark.parametrize("columns", ["col16", "col32", "matrix_free", "single_reduction"])
 def test_large_generated_case_against_reference(path, columns, monkeypatch):
     """BASELINE configs[3] at nx = 400 ... 2832 (84 k ... 4.04 M particles) against the UNMODIFIED compiled
     reference, whose digests / counts / strided samples tests/golden/make_large_golden.py recorded on the CPU
@@ -489,6 +489,9 @@ def test_large_generated_case_against_reference(path, columns, monkeypatch):
         monkeypatch.setenv("MPSB_FORCE_WIDE_COLUMNS", "1")
     # sweep A of the solve: stored entries (col16 / col32) or recomputed from positions (matrix_free)
     monkeypatch.setenv("MPSB_MATRIX_FREE", "1" if columns == "matrix_free" else "0")
+    # the opt-in Chronopoulos-Gear recurrence (one global reduction per iteration): same bars, iterations within 2 %
+    monkeypatch.setenv("MPSB_CG_SINGLE_REDUCTION", "1" if columns == "single_reduction" else "0")
+    monkeypatch.setenv("MPSB_CG_ITERATION_CAP", str(2 * int(z["cg_iterations"])))  # a solve that does not converge fails fast
     S, t, p, v = U.large_case(z)
     dev = capi.DeviceMPS(S, t, p, v)
     dev.load_initial_state()
@@ -521,19 +524,22 @@ def test_large_generated_case_against_reference(path, columns, monkeypatch):
           f"{abs(np.sqrt(np.sum(x * x)) - float(z['p_norm2'])) / float(z['p_norm2']):.2e}")
     assert st.ppe_columns_16bit == (0 if columns == "col32" else 1) and st.solve_in_cluster == 0
     assert st.ppe_matrix_free == (1 if columns == "matrix_free" else 0)
+    assert st.cg_single_reduction == (1 if columns == "single_reduction" else 0)
     # Iteration count. Eigen sums its dot products serially; that rounding alone delays the crossing of the eps
     # threshold against the SAME recurrence with tree sums: 999 vs 936 at nx = 400 under every ordering of the
     # unknowns (profiles/r2_cg_iteration_sensitivity_nx400.txt). The GPU sums in trees, so (a) it may need up to
     # 12 % fewer iterations than Eigen, never noticeably more, and (b) it must agree within 1 % with the
     # reference's PPE solved on the CPU by the identical recurrence with pairwise sums (second pin,
     # tests/golden/make_pairwise_iterations.py).
-    assert 0.88 * it_ref <= st.cg_iterations <= 1.02 * it_ref + 2
+    # (the single-reduction recurrence rounds its scalars differently again and is held to Eigen's count +- a few per cent
+    # only: 999 at nx = 400, as it happens Eigen's own 999, against 935 for the default loop)
+    assert 0.88 * it_ref <= st.cg_iterations <= (1.15 if columns == "single_reduction" else 1.02) * it_ref + 2
     import json
     import os
 
     pw = json.load(open(os.path.join(U.GOLDEN, "large_pairwise_iterations.json")))
     tag = path.split("large_nx")[-1][:-4]
-    if tag in pw:
+    if tag in pw and columns != "single_reduction":
         it_pw = pw[tag]["cg_iterations_pairwise"]
         print(f"   pairwise-sum CPU recurrence: {it_pw} iterations")
         assert abs(st.cg_iterations - it_pw) <= max(2, 0.01 * it_pw)
@@ -625,3 +631,33 @@ def test_matrix_free_grid_solve_on_the_goldens(path, monkeypatch):
         assert U.rel_err(got[name], after[name]) <= TOL, name
         assert U.elementwise_excess(got[name], after[name], TOL) <= 1.0, name
     dev.close()
+
+
+@pytest.mark.parametrize("path", U.golden_files(), ids=lambda p: p.split("/")[-1][:-4])
+def test_single_reduction_recurrence_on_the_goldens(path, monkeypatch):
+    """MPSB_CG_SINGLE_REDUCTION=1 (Chronopoulos-Gear: one global reduction and two grid-wide synchronisations per
+    iteration; opt-in, never the default) with the grid kernel forced, one whole step from the reference's state
+    against the reference's own next state: pressure / velocity / position within 1e-10. Its iteration count is NOT
+    within 2 % of the default recurrence: the recursively updated residual reaches the eps threshold 5-7 % later
+    (251 against 236 on dambreak_fine, 162 against 144 on hydrostatic) — asserted here as "no fewer,
+    at most 20 % more"."""
+    monkeypatch.setenv("MPSB_NO_CLUSTER_SOLVE", "1")
+    monkeypatch.setenv("MPSB_NO_STEP_GRAPH", "1")
+    z, before, after = U.load_golden(path)
+    S = C.load_case(U.golden_case(path))[0]
+    its = {}
+    for sr in ("0", "1"):
+        monkeypatch.setenv("MPSB_CG_SINGLE_REDUCTION", sr)
+        dev = capi.DeviceMPS(S, before["type"], before["position"], before["velocity"])
+        dev.upload(before)
+        dev.step_forward(bool(z["export"]))
+        got, st = dev.download(), dev.last_stats
+        assert st.cg_single_reduction == int(sr) and st.solve_in_cluster == 0
+        its[sr] = st.cg_iterations
+        assert st.cg_rel_residual <= 2.3e-16
+        assert np.array_equal(got["boundary_condition"], after["boundary_condition"])
+        for name in ("position", "velocity", "pressure", "minimum_pressure"):
+            assert U.rel_err(got[name], after[name]) <= TOL, (sr, name)
+            assert U.elementwise_excess(got[name], after[name], TOL) <= 1.0, (sr, name)
+        dev.close()
+    assert its["0"] - 2 <= its["1"] <= 1.20 * its["0"] + 2, its
