@@ -216,7 +216,10 @@ int mpsb_events(mpsb_handle* h, int kind, int32_t* ids, double* xyz, int capacit
  * exchanges travel over NVLink peer memory; NCCL carries the 4-byte cell keys, the counters and state syncs).
  * mpsb_step / mpsb_run_phase / mpsb_upload / mpsb_download are then collective; the inspection calls
  * (mpsb_get_neighbors, mpsb_get_ppe, mpsb_debug_spmv) are single-GPU only; mpsb_events lists the calling rank's events. `nccl_unique_id` is the 128-byte ncclUniqueId
- * produced on rank 0 and distributed by the host (torch.distributed / a launcher). */
+ * produced on rank 0 and distributed by the host (torch.distributed / a launcher).
+ * Cases below MPSB_MIN_SLAB_PARTICLES (default 32 768) are not sharded: attach succeeds, every rank keeps running the whole
+ * single-GPU step on the whole state (replicas, bit-identical, no communication) — a few thousand particles are a latency
+ * problem that cross-GPU exchanges only make worse. MPSB_MIN_SLAB_PARTICLES=0 shards every size. */
 int mpsb_comm_unique_id(void* out128);
 int mpsb_attach_comm(mpsb_handle* h, int rank, int world_size, const void* nccl_unique_id128);
 

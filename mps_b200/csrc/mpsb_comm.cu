@@ -14,6 +14,7 @@
 #include <nccl.h>
 
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 namespace {
@@ -93,6 +94,18 @@ extern "C" int mpsb_attach_comm(mpsb_handle* h, int rank, int world_size, const 
     if (h->sticky) return h->sticky;
     if (world_size == 1) return MPSB_OK;
     Params& P = h->P;
+    // Cases too small to shard profitably stay REPLICATED: every rank keeps running the whole single-GPU step (cluster
+    // solve, graph replay, no exchange of any kind) and holds the whole, bit-identical state. dambreak_fine (6 146
+    // particles) costs 1.8 ms per step on one GPU and 6.4 ms sharded over two (profiles/r1_v19_*): 236 CG iterations x
+    // a few cross-GPU latencies each buy nothing at that size. MPSB_MIN_SLAB_PARTICLES=0 forces sharding (tests do).
+    {
+        const char* ms = getenv("MPSB_MIN_SLAB_PARTICLES");
+        const int min_slab = ms ? atoi(ms) : 32768;
+        if (P.N < min_slab) {
+            h->replicated = world_size;
+            return MPSB_OK;
+        }
+    }
     if (!id128 || rank < 0 || rank >= world_size || world_size > MPSB_MAX_RANKS || (P.Np / 32) % world_size != 0 ||
         h->comm) {
         snprintf(h->err, sizeof h->err, "mpsb_attach_comm: bad rank/world (%d/%d; supported world sizes: 1, 2, 4, 8) "

@@ -224,6 +224,7 @@ struct mpsb_handle {
     // scratch for the radix sort
     int* block_hist; int block_hist_cap;
     unsigned long long* scan_status; int scan_status_cap; // look-back scan: one status word per scan tile, then the ticket counter
+    int replicated;         // > 0: mpsb_attach_comm was called with this world size but the case stays replicated (too small to shard)
     void* comm; int rank, world; // multi-GPU (mpsb_comm.cu): MpsbComm*, mirrors P.L.rank / P.L.world
     char* arena; size_t arena_bytes, arena_used; // peer-visible arrays (PeerLinks::arena)
     bool home_current;      // multi-GPU: HOME holds the latest state of EVERY particle (after an upload / a collective sync)

@@ -108,21 +108,24 @@ def test_cpp_host_runs_one_process_per_gpu(tmp_path):
 
     S = C.load_settings(C.case_paths("dambreak_fine")[0])
 
-    def launch(tag, world):
+    def launch(tag, world, **extra):
         d = tmp_path / tag
         d.mkdir()
         yml = C.write_settings_yaml(S, str(d / "settings.yml"), finish_time=8.5 * S.dt, output_interval=1.0)
         procs = []
         for rank in range(world):
             env = dict(os.environ, RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1",
-                       MASTER_PORT=str(29900 + os.getpid() % 90))
+                       MASTER_PORT=str(29900 + os.getpid() % 90), **extra)
             procs.append(subprocess.Popen([MPS_EXE, "-s", yml, "--quiet", "--state-out", str(d / "final.bin")], cwd=ROOT,
                                           stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env))
         outs = [p.communicate(timeout=300)[0] for p in procs]
         assert all(p.returncode == 0 for p in procs), outs
         return read_state(d / "final.bin")
 
-    one, two = launch("one", 1), launch("two", 2)
+    one, two = launch("one", 1), launch("two", 2, MPSB_MIN_SLAB_PARTICLES="0")  # 6 146 particles: force the sharded path
+    rep2 = launch("replicated", 2)  # default below 32 768 particles: replicas of the single-GPU step, bit for bit
+    for k in ("type", "boundary_condition", "position", "velocity", "pressure"):
+        assert np.array_equal(one[k], rep2[k]), k
     assert np.array_equal(one["type"], two["type"]) and np.array_equal(one["boundary_condition"], two["boundary_condition"])
     for k in ("position", "velocity", "pressure"):
         scale = max(float(np.abs(one[k]).max()), 1e-300)

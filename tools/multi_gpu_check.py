@@ -16,6 +16,7 @@ import sys
 
 import numpy as np
 
+os.environ.setdefault("MPSB_MIN_SLAB_PARTICLES", "0")  # this check is about the sharded path: shard the small cases too
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 
