@@ -157,6 +157,13 @@ def padded_rows(n):
     return (int(n) + 255) // 256 * 256
 
 
+def shard_block(n, rank, world):
+    """Particle ids [first, last) that the sharded transfers of `rank` move (mpsb_api.cu shard_block: the row-block split
+    applied to ids and clipped to n); the blocks of all ranks partition [0, n)."""
+    lo, hi = row_block(padded_rows(n), rank, world)
+    return min(n, lo), min(n, hi)
+
+
 class DeviceMPS:
     """One MPS simulation state resident on one B200."""
 

@@ -27,6 +27,54 @@ def test_row_blocks_partition_the_padded_rows():
         capi.row_block(100, 0, 2)
 
 
+def test_shard_blocks_partition_the_particle_ids():
+    """mpsb_upload_shard / mpsb_download_shard: every id belongs to exactly one rank's block, blocks are ordered and
+    only the last non-empty one can be short (it carries the padding)."""
+    for n in (0, 1, 255, 458, 2958, 6146, 84518, 4041990):
+        for world in (1, 2, 4, 8):
+            blocks = [capi.shard_block(n, r, world) for r in range(world)]
+            assert blocks[0][0] == 0 and blocks[-1][1] == n
+            covered = 0
+            for (a, b), (c, d) in zip(blocks, blocks[1:]):
+                assert a <= b == c <= d
+            for a, b in blocks:
+                covered += b - a
+            assert covered == n
+            per = capi.padded_rows(n) // world
+            assert all(b - a == per for a, b in blocks if b < n)
+
+
+def _gloo_shard_worker(rank, world, port, out):
+    """Host-side model of the sharded upload: each rank contributes its id block, an all-gather makes the array whole."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    n = 6146
+    full = np.arange(3 * n, dtype=np.float64).reshape(n, 3) * 0.5
+    per = capi.padded_rows(n) // world
+    lo, hi = capi.shard_block(n, rank, world)
+    mine = torch.zeros(per, 3, dtype=torch.float64)
+    mine[: hi - lo] = torch.from_numpy(full[lo:hi])          # what crosses "PCIe" on this rank
+    parts = [torch.zeros(per, 3, dtype=torch.float64) for _ in range(world)]
+    dist.all_gather(parts, mine)                               # what crosses "NVLink"
+    whole = torch.cat(parts)[:n].numpy()
+    with open(os.path.join(out, f"s{rank}"), "w") as f:
+        f.write("ok" if np.array_equal(whole, full) else "bad")
+    dist.destroy_process_group()
+
+
+def test_sharded_upload_model_gloo_world2(tmp_path):
+    import torch.multiprocessing as mp
+
+    port = 29100 + os.getpid() % 300
+    mp.spawn(_gloo_shard_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    assert [open(tmp_path / f"s{r}").read() for r in range(2)] == ["ok", "ok"]
+
+
 def _gloo_worker(rank, world, port, out):
     import torch.distributed as dist
 

@@ -103,6 +103,7 @@ def main():
     # (3) sharded transfers: a rank's mpsb_download_shard writes exactly its block of ids (and the right values);
     # after mpsb_upload_shard of the single-GPU state the device state is whole on every rank
     lo, hi = multi.shard_range()
+    assert (lo, hi) == capi.shard_block(len(t), rank, world), ((lo, hi), capi.shard_block(len(t), rank, world))
     part = {k: np.full_like(a[k], 7) for k in ("type", "position", "velocity", "pressure")}
     multi.download_into(part, shard=True)
     shard_ok = all(np.array_equal(part[k][lo:hi], a[k][lo:hi]) and (part[k][:lo] == 7).all() and (part[k][hi:] == 7).all()
