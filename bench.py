@@ -542,7 +542,8 @@ def run_gpu_arm(args):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": workload_config(args.nx, len(t), "1 GPU" if world == 1 else f"{world} y-slabs (PPE rows)"),
+            "config": workload_config(args.nx, len(t), "1 GPU" if world == 1 else f"{world} GPUs: every phase slab-decomposed by row blocks of the cell-major order "
+                                      "(halo particles, migration, Krylov exchanges over NVLink peer memory)"),
             "ppe_solve_ms_per_step": mean("ms_solve"), "cg_iterations_per_step": mean("cg_iterations"),
             "us_per_cg_iteration": 1e3 * solve_ms / max(1, sum(s["cg_iterations"] for s in stats)),
             "phase_ms_per_step": {k[3:]: mean(k) for k in ("ms_neighbors", "ms_explicit", "ms_collision", "ms_assemble",
@@ -552,6 +553,12 @@ def run_gpu_arm(args):
                                "C_direction": cyc[2] / max(1, sum(cyc)), "sync": cyc[3] / max(1, sum(cyc)),
                                "of": "rank 0, CTA 0, last solve (SM cycles)"},
             "sync_us_per_iteration": (cyc[3] / max(1, sum(cyc))) * 1e3 * solve_ms / max(1, sum(s["cg_iterations"] for s in stats)),
+            "solve_options": {"recurrence": "single reduction (Chronopoulos-Gear, opt-in)" if stats[-1].get("cg_single_reduction") else
+                              "textbook PCG = Eigen's loop (default)",
+                              "matrix_free": bool(stats[-1].get("ppe_matrix_free")),
+                              "l2_policy_of_matrix_stream": "evict_first + 16 MB evict_last for row blocks <= 2.5 M rows (multi-GPU splits); off at "
+                                                            "4 M rows on one GPU" if os.environ.get("MPSB_L2_RESIDENT_KB") is None else
+                                                            "MPSB_L2_RESIDENT_KB=" + os.environ["MPSB_L2_RESIDENT_KB"]},
             "parity_vs_1gpu": parity, "other_configs": other,
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
         }
