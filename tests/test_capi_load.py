@@ -55,3 +55,19 @@ def test_bad_arguments(lib):
     assert lib.mpsb_create(None, 0, None, None, None, 0, ct.byref(h)) == -1
     assert lib.mpsb_step(None, 0, None) == -1
     assert lib.mpsb_num_particles(None) == 0
+
+
+def test_every_environment_switch_the_library_reads_is_documented_in_the_header():
+    """include/mps_b200.h lists the MPSB_* switches; a getenv() in csrc/ or host/ that the header does not mention fails here."""
+    import glob
+    import os
+    import re
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    header = open(os.path.join(root, "include", "mps_b200.h")).read()
+    read = set()
+    for path in glob.glob(os.path.join(root, "mps_b200", "csrc", "*.cu*")) + glob.glob(os.path.join(root, "mps_b200", "host", "*.[ch]pp")):
+        read |= set(re.findall(r'getenv\("(MPSB_[A-Z0-9_]+)"\)', open(path).read()))
+    assert read, "no switches found: the pattern is stale"
+    missing = sorted(v for v in read if v not in header)
+    assert not missing, missing
