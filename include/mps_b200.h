@@ -23,6 +23,8 @@
  *   MPSB_CG_SINGLE_REDUCTION=1   grid solve with the Chronopoulos-Gear recurrence: one global reduction and two grid-wide
  *                                synchronisations per iteration instead of two and four; same Krylov space and stopping rule,
  *                                different rounding (held to 1e-10 / +-2 % iterations, not bit-identical); never the default
+ *   MPSB_CG_SMALL_ROWS=<rows>    row blocks of up to <rows> rows (default 1 300 000; twice that per rank on several GPUs) run the
+ *                                16-warp x 16-slot build of the grid solve instead of the 20 x 12 one (0 = never)
  *   MPSB_L2_RESIDENT_KB=<kb>     L2 policy of the solve's matrix stream: <kb> KiB travel as evict_last, the rest as evict_first
  *                                (default 16384; 0 = no policy), for row blocks of at most MPSB_L2_MAX_ROWS rows (2 500 000)
  * and by the host mirror (mps_b200/host): MPSB_DEVICE=<ordinal>, MPSB_CSV_FLOAT=gcc5.

@@ -31,6 +31,20 @@
 // ranks' p vectors, published by the same flag exchange that acts as the cross-GPU barrier.
 #include "mpsb_internal.cuh"
 
+// This file is compiled twice: as itself (ring geometry 20 warps x 2 stages x 12 slots, tuned at 4 M rows) and through
+// k_pcg_g16.cu (PCG_VARIANT 1: 16 warps x 2 x 16 slots, a whole ~28-slot slice in flight at once — faster for row blocks
+// of up to ~1.3 M rows, i.e. a rank's block of the 4 M case on 4 or 8 GPUs). Variant 0's launcher dispatches.
+#ifndef PCG_VARIANT
+#define PCG_VARIANT 0
+#endif
+#if PCG_VARIANT == 1
+#define mpsb_pcg_configure mpsb_pcg_configure_v1
+#define mpsb_launch_pcg mpsb_launch_pcg_v1
+#define mpsb_launch_spmv_probe mpsb_launch_spmv_probe_v1
+#define cg_threads cg1_threads
+#define cg_smem cg1_smem
+#endif
+
 #include <cfloat>
 #include <cstdlib>
 #include <cooperative_groups.h>
@@ -1274,6 +1288,7 @@ int mpsb_pcg_configure(mpsb_handle* h) {
     const mpsb_settings& s = h->P.s;
     const char* mf = getenv("MPSB_MATRIX_FREE");
     // part of the matrix stream kept L2-resident across iterations (L2Plan): MPSB_L2_RESIDENT_MB, 0 = off
+    h->cg_small_rows = getenv("MPSB_CG_SMALL_ROWS") ? atoi(getenv("MPSB_CG_SMALL_ROWS")) : 1300000;
     const char* l2kb = getenv("MPSB_L2_RESIDENT_KB");
     h->cg_l2_resident_kb = l2kb ? atoi(l2kb) : MPSB_L2_RESIDENT_KB_DEFAULT;
     h->cg_l2_max_rows    = getenv("MPSB_L2_MAX_ROWS") ? atoi(getenv("MPSB_L2_MAX_ROWS")) : MPSB_L2_MAX_ROWS_DEFAULT;
@@ -1284,7 +1299,17 @@ int mpsb_pcg_configure(mpsb_handle* h) {
 void mpsb_launch_pcg(mpsb_handle* h) {
     Params& P = h->P;
     const bool multi = P.L.world > 1;
+#if PCG_VARIANT == 0
     mpsb_launch_pcg_cluster(h); // small systems: one cluster, problem resident in shared memory; sets *cluster_done
+    // short row blocks: the 16-warp x 16-slot build of this file (k_pcg_g16.cu). Measured (profiles/r2_v13_ring_geometry.txt), us per
+    // iteration, 16 x 16 against 20 x 12: one GPU 32.1 / 35.3 at 0.25 M rows, 43.7 / 44.7 at 0.5 M, 70.0 / 73.3 at 1.0 M, 141.6 / 142.6
+    // at 2.0 M, 288.1 / 285.2 at 4.0 M (its 512-thread vector sweeps are slower); two GPUs 49.3 / 53.3 at 0.5 M rows per rank,
+    // 76.8 / 85.8 at 1.0 M, 142.1 / 152.0 at 2.0 M. Hence: up to cg_small_rows on one GPU, up to twice that per rank on several.
+    if (P.Np / (multi ? P.L.world : 1) <= (multi ? 2 : 1) * h->cg_small_rows && !h->cg_matrix_free) {
+        mpsb_launch_pcg_v1(h);
+        return;
+    }
+#endif
     // one 32-row slice per warp at least; never more CTAs than can be co-resident (cooperative launch)
     int want = mpsb_div_up(P.Np / 32 / (multi ? P.L.world : 1), PCG_WARPS);
     int grid = want < h->cg_max_blocks ? want : h->cg_max_blocks;

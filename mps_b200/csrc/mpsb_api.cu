@@ -235,7 +235,7 @@ int mpsb_create(const mpsb_settings* settings, int64_t n, const int32_t* type, c
     CKC(dalloc(&h->block_hist, (size_t) h->block_hist_cap));
     h->scan_status_cap = h->block_hist_cap / 4096 + 2;
     CKC(dalloc(&h->scan_status, (size_t) h->scan_status_cap + 1)); // [cap] = the ticket counter
-    if (mpsb_neighbors_configure(h) != 0 || mpsb_pcg_configure(h) != 0) {
+    if (mpsb_neighbors_configure(h) != 0 || mpsb_pcg_configure(h) != 0 || mpsb_pcg_configure_v1(h) != 0) {
         snprintf(g_create_error, sizeof g_create_error, "mpsb_create: PCG kernel cannot be made resident");
         mpsb_destroy(h);
         return MPSB_ERR_CUDA;

@@ -201,6 +201,8 @@ struct mpsb_handle {
     int cg_max_blocks;      // cooperative grid limit for the PCG kernel
     int cg_threads;
     int cg_smem;            // dynamic shared memory of the PCG kernel
+    int cg1_threads, cg1_smem; // the same for the 16-warp x 16-slot build (k_pcg_g16.cu), used for row blocks <= cg_small_rows
+    int cg_small_rows;      // MPSB_CG_SMALL_ROWS (default 1 300 000)
     int cg_iteration_cap;   // diagnostic: stop the solve after this many iterations (0 = Eigen's 2N)
     int cg_l2_resident_kb;  // L2 policy of the matrix stream (k_pcg.cu L2Plan): KiB kept with evict_last, the rest evict_first; 0 = off
     int cg_l2_max_rows;     // ... applied to row blocks of at most this many rows
@@ -249,6 +251,8 @@ void mpsb_launch_dirichlet(mpsb_handle* h);
 void mpsb_launch_pressure_post(mpsb_handle* h);
 void mpsb_launch_pcg(mpsb_handle* h);                   // k_pcg.cu
 int mpsb_pcg_configure(mpsb_handle* h);
+int mpsb_pcg_configure_v1(mpsb_handle* h);              // k_pcg_g16.cu: the second ring geometry of the same kernel
+void mpsb_launch_pcg_v1(mpsb_handle* h);
 void mpsb_launch_spmv_probe(mpsb_handle* h, int matrix_free); // diagnostic: one sweep A, cg_p -> cg_ap
 int mpsb_pcg_cluster_configure(mpsb_handle* h);         // k_pcg_cluster.cu
 int mpsb_launch_pcg_cluster(mpsb_handle* h);

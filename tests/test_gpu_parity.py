@@ -257,6 +257,32 @@ def test_scaled_dambreak_nonkrylov_phases_bitwise_and_cg_properties(nx):
     dev.close()
 
 
+def test_both_ring_geometries_of_the_grid_solve_agree_with_the_oracle(monkeypatch):
+    """The persistent PCG kernel is built twice (k_pcg.cu: 20 warps x 2 stages x 12 slots; k_pcg_g16.cu: 16 x 2 x 16,
+    the default for row blocks of up to MPSB_CG_SMALL_ROWS = 1.3 M rows). Row sums follow slot order in both; only the
+    partition of the reductions differs, so the two solves agree with the oracle's Eigen-order CG to 1e-10 and with
+    each other in the iteration count (+- 2)."""
+    S, t, p, v = C.scaled_dambreak(200)
+    orc = R.OracleMPS(S.to_c(), t, p, v)
+    for _, _, ophs in PHASE_MAP[:9]:
+        for ph in ophs:
+            orc.phase(ph)
+    want = orc.get_state(["pressure"])["pressure"]
+    its = []
+    for small_rows in ("0", "1300000"):
+        monkeypatch.setenv("MPSB_CG_SMALL_ROWS", small_rows)
+        dev = capi.DeviceMPS(S, t, p, v)
+        dev.load_initial_state()
+        for name, dph, _ in PHASE_MAP[:8]:
+            dev.run_phase(dph)
+        st = dev.run_phase(capi.PH_SOLVE)
+        assert st.solve_in_cluster == 0 and st.cg_rel_residual <= 2.3e-16
+        its.append(st.cg_iterations)
+        assert U.rel_err(dev.download(["pressure"])["pressure"], want) <= TOL, small_rows
+        dev.close()
+    assert abs(its[0] - its[1]) <= 2, its
+
+
 def test_16_bit_and_32_bit_column_streams_give_identical_solves(monkeypatch):
     """The solve streams columns as 16-bit offsets from the slice's first row when they all fit, else as
     int32 (matrix_kernel decides per assembly). Same arithmetic in the same order -> bitwise equal pressure,
