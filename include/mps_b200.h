@@ -245,6 +245,35 @@ int mpsb_debug_spmv(mpsb_handle* h, const double* x, double* y, int matrix_free)
 /* Counters since create: kernel launches issued by this library on this handle. */
 int64_t mpsb_launch_count(const mpsb_handle* h);
 
+/* --- for callers that must not allocate ----------------------------------------------------------------------
+ * No counterpart in the reference (it has no device code and no allocator to avoid); the value computed is the one
+ * of getCourantNumber (src/mps.cpp:547-571), bit-identical to mpsb_run_phase with MPSB_PH_COURANT.
+ *
+ * Everything above works on a handle, and a handle is made of cudaMalloc'ed arrays. This one call is for programs that
+ * hold a particle state in device memory of their own and cannot let a library allocate when they call it: a host that
+ * gave all device memory to its own pool, a caller inside a section where cudaMalloc's implicit device-wide
+ * synchronisation would stall its other streams, a watchdog that only wants to know whether a live state still obeys the
+ * CFL limit. It performs no cudaMalloc / cudaFree and calls no allocating routine, and it needs no handle.
+ *
+ * Inputs and the output are DEVICE pointers on CUDA device `device`: d_type int32[n], d_velocity packed xyz double[3n],
+ * d_courant one double. The kernel is queued on `cuda_stream` (a cudaStream_t passed as void*; NULL = the default
+ * stream) and the call returns WITHOUT synchronising: *d_courant is valid once that stream has reached this point.
+ * Only particles of type MPSB_FLUID count; n = 0 gives 0.0.
+ *
+ * The kernel's scratch memory (one partial maximum per thread block + a ticket counter) is a fixed array inside the
+ * library image, MPSB_STATIC_SCRATCH_BYTES on every GPU the library is loaded on, held until the process ends. Hence:
+ *   - n may not exceed MPSB_STATIC_MAX_PARTICLES; a larger n returns MPSB_ERR_ARG, launches nothing and says so in error_text;
+ *   - all calls on one GPU share the array, and it keeps the previous call's contents. The call itself clears what has to
+ *     start at zero, so calls that follow one another on the GPU are independent; calls that may OVERLAP on the GPU
+ *     (two streams with no ordering between them, two host threads) race on it — serialise them;
+ *   - the first call on each device looks up the array's device address (once per device); make that first call before,
+ *     not during, any stream capture.
+ * error_text (may be NULL) receives a message of at most error_capacity bytes when the return value is not MPSB_OK. */
+#define MPSB_STATIC_MAX_PARTICLES 67108864LL
+#define MPSB_STATIC_SCRATCH_BYTES 262400
+int mpsb_courant_static(const int32_t* d_type, const double* d_velocity, int64_t n, double dt, double particle_distance,
+                        int device, void* cuda_stream, double* d_courant, char* error_text, int error_capacity);
+
 #ifdef __cplusplus
 }
 #endif

@@ -28,7 +28,7 @@ EXPORTED = [
     "mpsb_upload", "mpsb_download", "mpsb_num_particles", "mpsb_get_neighbors", "mpsb_get_ppe", "mpsb_events",
     "mpsb_comm_unique_id", "mpsb_attach_comm", "mpsb_upload_device", "mpsb_launch_count", "mpsb_set_stream",
     "mpsb_debug_cg_cycles", "mpsb_debug_cg_block_cycles", "mpsb_debug_spmv", "mpsb_host_alloc", "mpsb_host_free",
-    "mpsb_upload_shard", "mpsb_download_shard", "mpsb_shard_range",
+    "mpsb_upload_shard", "mpsb_download_shard", "mpsb_shard_range", "mpsb_courant_static",
 ]
 
 
@@ -115,6 +115,8 @@ def load_library():
     lib.mpsb_set_stream.argtypes = [vp, vp]
     lib.mpsb_launch_count.restype = i64
     lib.mpsb_launch_count.argtypes = [vp]
+    lib.mpsb_courant_static.restype = i32
+    lib.mpsb_courant_static.argtypes = [vp, vp, i64, ct.c_double, ct.c_double, i32, vp, vp, ct.c_char_p, i32]
     _lib = lib
     return lib
 
