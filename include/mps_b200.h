@@ -19,7 +19,8 @@
  *   MPSB_FORCE_WIDE_COLUMNS=1    stream int32 PPE columns even when 16-bit offsets fit
  *   MPSB_CG_ITERATION_CAP=<n>    stop the solve after n iterations (profiling a bounded solve)
  *   MPSB_MATRIX_FREE=0|1         sweep A of the grid solve streams the stored off-diagonals (0) or recomputes them from
- *                                positions (1; 2-D cases only)
+ *                                positions (1; 2-D cases on ONE GPU only: with an attached multi-GPU group the switch is
+ *                                ignored and ppe_matrix_free reports 0, because positions of halo columns are not exchanged)
  *   MPSB_CG_SINGLE_REDUCTION=1   grid solve with the Chronopoulos-Gear recurrence: one global reduction and two grid-wide
  *                                synchronisations per iteration instead of two and four; same Krylov space and stopping rule,
  *                                different rounding (held to 1e-10 / +-2 % iterations, not bit-identical); never the default
@@ -209,7 +210,9 @@ int mpsb_get_neighbors(mpsb_handle* h, int64_t* row_start, int32_t* ids, double*
 int mpsb_get_ppe(mpsb_handle* h, int64_t* row_start, int32_t* col, double* val, double* rhs,
                  int64_t capacity, int64_t* nnz);
 /* Ids of particles behind the last step's debug-log events (src/mps.cpp:405-410, 655-663).
- * kind 0 = ghosted (xyz = position at the time, 3 doubles each), 1 = Dirichlet-unconnected. */
+ * kind 0 = ghosted (xyz = position at the time, 3 doubles each), 1 = Dirichlet-unconnected.
+ * With an attached multi-GPU group *count and the ids are those of the CALLING rank's rows only (the counters in
+ * mpsb_step_stats are sums over the ranks); the union over the ranks is the single-GPU list. */
 int mpsb_events(mpsb_handle* h, int kind, int32_t* ids, double* xyz, int capacity, int* count);
 
 /* --- multi-GPU (one process per GPU; slab decomposition by rows of the cell-major order) ---------------------

@@ -1299,13 +1299,16 @@ int mpsb_pcg_configure(mpsb_handle* h) {
 void mpsb_launch_pcg(mpsb_handle* h) {
     Params& P = h->P;
     const bool multi = P.L.world > 1;
+    // The matrix-free sweep gathers positions (row_xy) of halo columns, and row_xy holds only this rank's own rows (matrix_kernel
+    // writes [row_lo, row_hi); it is not in the peer arena and no halo push fills it): one GPU only, several GPUs stream the stored entries.
+    const int mfree = multi ? 0 : h->cg_matrix_free;
 #if PCG_VARIANT == 0
     mpsb_launch_pcg_cluster(h); // small systems: one cluster, problem resident in shared memory; sets *cluster_done
     // short row blocks: the 16-warp x 16-slot build of this file (k_pcg_g16.cu). Measured (profiles/r2_v13_ring_geometry.txt), us per
     // iteration, 16 x 16 against 20 x 12: one GPU 32.1 / 35.3 at 0.25 M rows, 43.7 / 44.7 at 0.5 M, 70.0 / 73.3 at 1.0 M, 141.6 / 142.6
     // at 2.0 M, 288.1 / 285.2 at 4.0 M (its 512-thread vector sweeps are slower); two GPUs 49.3 / 53.3 at 0.5 M rows per rank,
     // 76.8 / 85.8 at 1.0 M, 142.1 / 152.0 at 2.0 M. Hence: up to cg_small_rows on one GPU, up to twice that per rank on several.
-    if (P.Np / (multi ? P.L.world : 1) <= (multi ? 2 : 1) * h->cg_small_rows && !h->cg_matrix_free) {
+    if (P.Np / (multi ? P.L.world : 1) <= (multi ? 2 : 1) * h->cg_small_rows && !mfree) {
         mpsb_launch_pcg_v1(h);
         return;
     }
@@ -1317,7 +1320,6 @@ void mpsb_launch_pcg(mpsb_handle* h) {
     int max_blocks = h->cg_max_blocks;
     if (multi) cudaMemsetAsync(P.L.arrive, 0, 2 * sizeof(unsigned long long), h->stream); // both arrival counters
     int cap = h->cg_iteration_cap;
-    int mfree = h->cg_matrix_free;
     int resident_kb = (P.Np / (multi ? P.L.world : 1) <= h->cg_l2_max_rows) ? h->cg_l2_resident_kb : 0;
     void* args[] = {(void*) &P, (void*) &max_blocks, (void*) &cap, (void*) &mfree, (void*) &resident_kb};
     const bool sr = h->cg_single_reduction && !mfree;

@@ -786,6 +786,14 @@ int mpsb_events(mpsb_handle* h, int kind, int32_t* ids, double* xyz, int capacit
     if (h->sticky) return h->sticky;
     CK(h, cudaSetDevice(h->device));
     int n = kind == 0 ? h->host_stats.n_ghosted : h->host_stats.n_unconnected;
+    if (h->world > 1) {
+        // host_stats holds the SUM over the ranks (combine_stats_kernel); the event buffers hold this rank's events only,
+        // indexed by this rank's own counter, which the combine left untouched in *P.stats
+        DevStats own;
+        CK(h, cudaStreamSynchronize(h->stream));
+        CK(h, cudaMemcpy(&own, h->P.stats, sizeof own, cudaMemcpyDeviceToHost));
+        n = kind == 0 ? own.n_ghosted : own.n_unconnected;
+    }
     n     = std::min(n, h->P.ev_cap);
     *count = n;
     int m = std::min(n, capacity);

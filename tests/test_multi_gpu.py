@@ -134,12 +134,32 @@ def test_split_solve_matches_single_gpu(case, steps):
     assert r.returncode == 0 and lines, r.stdout[-2000:] + r.stderr[-2000:]
     rep = json.loads(lines[-1])
     assert rep["ok"] and rep["ranks_bit_identical"] and rep["flags_equal"] and rep["counters_equal"], rep
+    assert rep["event_ids_equal"], rep  # every rank lists its own rows' events; their union is the 1-GPU list
     if case == "dambreak@200":
         assert rep["collisions_replayed"] > 0, rep  # the cross-rank collision replay really ran
     if case == "dambreak@320":
         assert rep["particles_ghosted"] > 0, rep
     if case.startswith("nx="):
         assert rep["vs_compiled_reference"]["ok"], rep
+
+
+@pytest.mark.gpu
+def test_matrix_free_switch_is_ignored_on_several_gpus():
+    """MPSB_MATRIX_FREE=1 recomputes the off-diagonals from positions, and positions of halo columns are not exchanged:
+    an attached handle must keep streaming the stored entries (ppe_matrix_free 0) and stay at parity with the
+    single-GPU handle of the same process, which does run matrix-free."""
+    if _gpu_count() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    port = 29600 + (os.getpid() + 7) % 300
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+           "--master-addr", "127.0.0.1", "--master-port", str(port),
+           os.path.join(ROOT, "tools", "multi_gpu_check.py"), "nx=400", "2"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600,
+                       env=dict(os.environ, MPSB_MATRIX_FREE="1", MPSB_NO_CLUSTER_SOLVE="1"))
+    lines = [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
+    assert r.returncode == 0 and lines, r.stdout[-2000:] + r.stderr[-2000:]
+    rep = json.loads(lines[-1])
+    assert rep["ok"] and rep["matrix_free_on_multi"] == 0 and rep["vs_compiled_reference"]["ok"], rep
 
 
 @pytest.mark.gpu

@@ -68,7 +68,8 @@ def main():
         single.step_forward(False)
     worst = {"pressure": 0.0, "velocity": 0.0, "position": 0.0}
     flags_equal, iters = True, []
-    collisions = ghosted = 0
+    collisions = ghosted = matrix_free_multi = 0
+    events_equal = True
     for k in range(steps):
         # teacher-forced per step from the single-GPU state (the dynamics are chaotic)
         st = single.download(["type", "position", "velocity", "pressure"])
@@ -83,6 +84,14 @@ def main():
         iters.append((multi.last_stats.cg_iterations, single.last_stats.cg_iterations))
         collisions += multi.last_stats.n_collisions
         ghosted += multi.last_stats.n_ghosted
+        # the debug-log events: each rank lists the events of ITS rows; their union is the single-GPU list
+        for kind in (0, 1):
+            mine_ev = [None] * world
+            dist.all_gather_object(mine_ev, [int(i) for i in multi.events(kind)[0]])
+            union = sorted(i for part in mine_ev for i in part)
+            events_equal &= union == sorted(int(i) for i in single.events(kind)[0])
+            events_equal &= len(union) == (multi.last_stats.n_ghosted if kind == 0 else multi.last_stats.n_unconnected)
+        matrix_free_multi |= multi.last_stats.ppe_matrix_free
         flags_equal &= (multi.last_stats.n_collisions, multi.last_stats.n_ghosted) == \
                        (single.last_stats.n_collisions, single.last_stats.n_ghosted)
     # (2) free-running: the N-rank handle carries its own state from step to step (halo particles and migration
@@ -118,13 +127,13 @@ def main():
     dist.broadcast(ref, src=0)
     same = torch.tensor([int(torch.equal(mine.view(torch.int64), ref.view(torch.int64)))], device="cuda")
     dist.all_reduce(same, op=dist.ReduceOp.MIN)
-    ok = bool(same.item()) and flags_equal and counters_equal and shard_ok and all(x <= 1e-10 for x in worst.values()) and \
+    ok = bool(same.item()) and flags_equal and counters_equal and events_equal and not matrix_free_multi and shard_ok and all(x <= 1e-10 for x in worst.values()) and \
         all(x <= 1e-8 for x in free.values()) and (vs_reference is None or vs_reference["ok"])
     okt = torch.tensor([int(ok)], device="cuda")
     dist.all_reduce(okt, op=dist.ReduceOp.MIN)
     if rank == 0:
         print(json.dumps({"case": what, "world": world, "steps": steps, "ranks_bit_identical": bool(same.item()),
-                          "flags_equal": flags_equal, "counters_equal": counters_equal, "sharded_transfers_ok": bool(shard_ok), "max_rel_diff_vs_single_gpu": worst,
+                          "flags_equal": flags_equal, "counters_equal": counters_equal, "event_ids_equal": events_equal, "matrix_free_on_multi": int(matrix_free_multi), "sharded_transfers_ok": bool(shard_ok), "max_rel_diff_vs_single_gpu": worst,
                           "free_run_3_steps_max_rel_diff": free, "vs_compiled_reference": vs_reference,
                           "collisions_replayed": collisions, "particles_ghosted": ghosted,
                           "cg_iterations_multi_vs_single": iters[-3:], "ok": bool(okt.item())}), flush=True)
