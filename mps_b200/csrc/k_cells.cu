@@ -7,6 +7,7 @@
 // it, i.e. the same traversal order. Ghosts get the maximum key and sink to the tail
 // (the reference skips them, bucket.cpp:37-38).
 #include "mpsb_internal.cuh"
+#include <cstdio>
 
 namespace {
 
@@ -97,6 +98,12 @@ __device__ __forceinline__ unsigned long long scan_pack(unsigned long long epoch
     return ((epoch & 0x3FFFFFFFull) << 34) | (flag << 32) | (unsigned long long) (unsigned) v;
 }
 
+__device__ __forceinline__ unsigned long long scan_timer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
 __global__ void __launch_bounds__(SCAN_THREADS) scan_lookback_kernel(int* __restrict__ data, int n, int ntiles,
                                                                     unsigned long long* __restrict__ status,
                                                                     unsigned long long* __restrict__ ticket) {
@@ -145,8 +152,18 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_lookback_kernel(int* __rest
             const int j = look - lane;
             unsigned long long w = scan_pack(epoch, SCAN_PREFIX, 0); // lanes before tile 0: an empty inclusive prefix
             if (j >= 0) {
+                // A predecessor publishes within microseconds (tiles are handed out in ticket order, so it is already
+                // running). A status word that never turns up means a launch with another tile count or a ticket out
+                // of step with the epochs: fail loudly (trap -> MPSB_ERR_CUDA on the host) instead of hanging the GPU.
+                unsigned spins = 0;
+                unsigned long long t0 = 0ull;
                 do {
                     w = st[j];
+                    if ((++spins & 4095u) == 0u) {
+                        const unsigned long long now = scan_timer_ns();
+                        if (t0 == 0ull) t0 = now;
+                        else if (now - t0 > 5000000000ull) __trap();
+                    }
                 } while ((w >> 34) != (epoch & 0x3FFFFFFFull) || ((w >> 32) & 3ull) == 0ull);
             }
             const unsigned has_prefix = __ballot_sync(0xffffffffu, ((w >> 32) & 3ull) == SCAN_PREFIX);
@@ -555,6 +572,12 @@ void mpsb_launch_scatter_all_rows(mpsb_handle* h) {
 void mpsb_launch_cell_build(mpsb_handle* h, bool scatter_first) {
     Params& P   = h->P;
     int N       = P.N;
+    if (mpsb_div_up(RADIX * mpsb_div_up(N, SORT_TILE), SCAN_TILE) > h->scan_status_cap) { // one status word per scan tile
+        snprintf(h->err, sizeof h->err, "cell build: %d scan tiles exceed the %d status words of this handle",
+                 mpsb_div_up(RADIX * mpsb_div_up(N, SORT_TILE), SCAN_TILE), h->scan_status_cap);
+        h->sticky = MPSB_ERR_ARG;
+        return;
+    }
     if (h->world > 1) {
         const int grid = mpsb_div_up(N, 256), tiles = mpsb_div_up(N, SORT_TILE);
         const int scan_tiles = mpsb_div_up(RADIX * tiles, SCAN_TILE);

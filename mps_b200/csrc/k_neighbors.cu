@@ -345,15 +345,29 @@ void mpsb_launch_neighbors(mpsb_handle* h) {
 }
 
 namespace {
-__global__ void ghost_ratio_from_home_kernel(Params P) {
+// only_new: touch only particles that are Ghost now and were not before the upload (P.mark, ghost_mark_kernel)
+__global__ void ghost_ratio_from_home_kernel(Params P, int only_new) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < P.N && P.H.type[i] == MPSB_GHOST) P.ghost_ratio[i] = P.H.ratio[i];
+    if (i < P.N && P.H.type[i] == MPSB_GHOST && !(only_new && P.mark[i])) P.ghost_ratio[i] = P.H.ratio[i];
+}
+__global__ void ghost_mark_kernel(Params P) { // P.mark is per-phase scratch (collision replay, Dirichlet): free between calls
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < P.N) P.mark[i] = P.H.type[i] == MPSB_GHOST;
 }
 } // namespace
 
-void mpsb_launch_ghost_ratio_from_home(mpsb_handle* h) {
+// An upload that carries the ratio sets every Ghost's recorded sum to its uploaded ratio. An upload of the types alone must
+// not: a particle that turned Ghost in a step without a number-density pass still has its pre-ghost ratio in HOME, and the
+// sum mpsb_record_ghost_ratio froze for it is the value the reference reports. Only a particle the upload itself turns
+// Ghost takes its HOME ratio (mark before the copy with mpsb_launch_ghost_mark, refresh after it with only_new).
+void mpsb_launch_ghost_ratio_from_home(mpsb_handle* h, bool only_new) {
     Params& P = h->P;
-    MPSB_LAUNCH(h, ghost_ratio_from_home_kernel, mpsb_div_up(P.N, 256), 256, 0, P);
+    MPSB_LAUNCH(h, ghost_ratio_from_home_kernel, mpsb_div_up(P.N, 256), 256, 0, P, only_new ? 1 : 0);
+}
+
+void mpsb_launch_ghost_mark(mpsb_handle* h) {
+    Params& P = h->P;
+    MPSB_LAUNCH(h, ghost_mark_kernel, mpsb_div_up(P.N, 256), 256, 0, P);
 }
 
 void mpsb_launch_number_density(mpsb_handle* h) {

@@ -304,6 +304,8 @@ int mpsb_upload(mpsb_handle* h, uint32_t mask, const mpsb_fields* f) {
     size_t N = (size_t) h->P.N;
     Home& H  = h->P.H;
     cudaStream_t st = h->stream;
+    const bool types_only = (mask & MPSB_F_TYPE) && f->type && !((mask & MPSB_F_NUMBER_DENSITY_RATIO) && f->number_density_ratio);
+    if (types_only && N > 0) mpsb_launch_ghost_mark(h); // see mpsb_launch_ghost_ratio_from_home
 #define UP(bit, dst, src, bytes)                                                                  \
     if ((mask & (bit)) && (src)) CK(h, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, st))
     UP(MPSB_F_TYPE, H.type, f->type, sizeof(int) * N);
@@ -315,7 +317,7 @@ int mpsb_upload(mpsb_handle* h, uint32_t mask, const mpsb_fields* f) {
     UP(MPSB_F_NUMBER_DENSITY_RATIO, H.ratio, f->number_density_ratio, sizeof(double) * N);
     UP(MPSB_F_BOUNDARY_CONDITION, H.bc, f->boundary_condition, sizeof(int) * N);
 #undef UP
-    if ((mask & (MPSB_F_NUMBER_DENSITY_RATIO | MPSB_F_TYPE)) && N > 0) mpsb_launch_ghost_ratio_from_home(h);
+    if ((mask & (MPSB_F_NUMBER_DENSITY_RATIO | MPSB_F_TYPE)) && N > 0) mpsb_launch_ghost_ratio_from_home(h, types_only);
     if (h->have_lists && N > 0) mpsb_launch_gather_all(h); // keep the sorted working set in step (every row, on every rank)
     h->home_current = true;
     CK(h, cudaStreamSynchronize(st));
@@ -392,6 +394,8 @@ int mpsb_upload_shard(mpsb_handle* h, uint32_t mask, const mpsb_fields* f) {
     Home& H = h->P.H;
     cudaStream_t st = h->stream;
     uint32_t present = 0;
+    const bool types_only = (mask & MPSB_F_TYPE) && f->type && !((mask & MPSB_F_NUMBER_DENSITY_RATIO) && f->number_density_ratio);
+    if (types_only && h->P.N > 0) mpsb_launch_ghost_mark(h); // see mpsb_launch_ghost_ratio_from_home
 #define UP(bit, dst, src, per, T)                                                                                   \
     if ((mask & (bit)) && (src)) {                                                                                  \
         present |= (bit);                                                                                           \
@@ -408,7 +412,7 @@ int mpsb_upload_shard(mpsb_handle* h, uint32_t mask, const mpsb_fields* f) {
 #undef UP
     if (int rc = mpsb_comm_allgather_home(h, present)) return rc; // the other ranks' blocks arrive over NVLink
     const size_t N = (size_t) h->P.N;
-    if ((present & (MPSB_F_NUMBER_DENSITY_RATIO | MPSB_F_TYPE)) && N > 0) mpsb_launch_ghost_ratio_from_home(h);
+    if ((present & (MPSB_F_NUMBER_DENSITY_RATIO | MPSB_F_TYPE)) && N > 0) mpsb_launch_ghost_ratio_from_home(h, types_only);
     if (h->have_lists && N > 0) mpsb_launch_gather_all(h);
     h->home_current = true;
     CK(h, cudaStreamSynchronize(st));

@@ -240,7 +240,8 @@ void mpsb_launch_scatter_all(mpsb_handle* h);           // SORTED -> HOME
 void mpsb_launch_neighbors(mpsb_handle* h);             // k_neighbors.cu
 int mpsb_neighbors_configure(mpsb_handle* h);           // shared-memory opt-in of the tiled build
 void mpsb_launch_number_density(mpsb_handle* h);
-void mpsb_launch_ghost_ratio_from_home(mpsb_handle* h); // after an upload: a Ghost's recorded sum is its uploaded ratio
+void mpsb_launch_ghost_ratio_from_home(mpsb_handle* h, bool only_new); // after an upload: a Ghost's recorded sum is its uploaded ratio (only_new: only particles the upload turned Ghost)
+void mpsb_launch_ghost_mark(mpsb_handle* h); // before a types-only upload: remember who is Ghost already (P.mark)
 void mpsb_launch_explicit(mpsb_handle* h);              // k_explicit.cu
 void mpsb_launch_collision(mpsb_handle* h);
 void mpsb_launch_gradient_move(mpsb_handle* h);

@@ -687,3 +687,33 @@ def test_single_reduction_recurrence_on_the_goldens(path, monkeypatch):
             assert U.elementwise_excess(got[name], after[name], TOL) <= 1.0, (sr, name)
         dev.close()
     assert its["0"] - 2 <= its["1"] <= 1.20 * its["0"] + 2, its
+
+
+def test_types_only_upload_keeps_the_ratio_recorded_when_a_particle_left_the_domain():
+    """A particle that turns Ghost keeps, in the reference, the neighbour list it had (src/mps.cpp:655-665), so its
+    number-density ratio is frozen at the sum over that list; the device records that sum at the moment of ghosting.
+    An upload of the types alone (the teacher-forced pattern of tools/multi_gpu_check.py) must not replace the
+    recorded sum by the pre-ghost ratio still sitting in the particle array when the step ran no number-density pass."""
+    path = [p for p in U.golden_files("dambreak") if p.endswith("step0430.npz")][0]  # particle 272 leaves with one neighbour left
+    z, before, after = U.load_golden(path)
+    S, _, _, _ = C.load_case("dambreak")
+
+    def run(reupload_types):
+        dev = capi.DeviceMPS(S, before["type"], before["position"], before["velocity"])
+        dev.upload(before)
+        dev.step_forward(False)  # no number-density pass at the end of this step
+        assert dev.last_stats.n_ghosted == 1
+        if reupload_types:
+            dev.upload({"type": dev.download(["type"])["type"]})
+        dev.run_phase(capi.PH_NUMBER_DENSITY)
+        out = dev.download(["type", "number_density_ratio"])
+        dev.close()
+        return out
+
+    a, b = run(False), run(True)
+    ghost = np.flatnonzero((a["type"] == C.GHOST) & (before["type"] != C.GHOST))
+    assert len(ghost) == 1 and np.array_equal(a["type"], after["type"])
+    assert np.array_equal(a["number_density_ratio"], b["number_density_ratio"])
+    ghosts = a["type"] == C.GHOST
+    assert np.array_equal(a["number_density_ratio"][ghosts], after["number_density_ratio"][ghosts])  # the compiled reference's values, bit for bit
+    assert a["number_density_ratio"][ghost[0]] != before["number_density_ratio"][ghost[0]]  # the case does tell the two apart
