@@ -224,7 +224,11 @@ int mpsb_events(mpsb_handle* h, int kind, int32_t* ids, double* xyz, int capacit
  * produced on rank 0 and distributed by the host (torch.distributed / a launcher).
  * Cases below MPSB_MIN_SLAB_PARTICLES (default 32 768) are not sharded: attach succeeds, every rank keeps running the whole
  * single-GPU step on the whole state (replicas, bit-identical, no communication) — a few thousand particles are a latency
- * problem that cross-GPU exchanges only make worse. MPSB_MIN_SLAB_PARTICLES=0 shards every size. */
+ * problem that cross-GPU exchanges only make worse. MPSB_MIN_SLAB_PARTICLES=0 shards every size.
+ * Collision capacity of a sharded handle: each rank may record at most min(C / 8, 16 384) colliding pairs of its own rows per
+ * step, C = the single-GPU candidate capacity (the power of two >= max(1024, n / 4)); the records of all ranks are then
+ * replayed in the reference's serial order by one thread on every rank. More pairs than that on one rank end the step with
+ * MPSB_ERR_CAPACITY on every rank (the same state may still fit the single-GPU path, whose limit is C). */
 int mpsb_comm_unique_id(void* out128);
 int mpsb_attach_comm(mpsb_handle* h, int rank, int world_size, const void* nccl_unique_id128);
 
