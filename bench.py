@@ -385,9 +385,102 @@ def parity_vs_one_gpu(dev, S, t, p, v, local, world):
     okt = torch.tensor([int(ok)], device="cuda")
     dist.all_reduce(okt, op=dist.ReduceOp.MIN)
     return {"ok": bool(okt.item()), "ranks_bit_identical": bool(same.item()), "flags_equal": flags, "max_rel": worst,
-            "cg_iterations_n_gpus_vs_1": list(it), "tolerance": 1e-10,
-            "how": "one step from the initial state; N-rank handle vs a single-GPU handle of the same library on "
-                   "every rank's own device; the single-GPU path is pinned to the reference by the -m gpu tests"}
+            "cg_iterations_n_gpus_vs_1": list(it), "tolerance": 1e-10}
+
+
+def parity_in_motion(rank, world, local):
+    """N > 1, before the timed region: the slab path with things happening in it, on this run's own ranks
+    (tools/multi_gpu_check.py, the checks of tests/test_multi_gpu.py): dambreak after 200 steps (collisions replayed
+    across ranks), after 320 steps (particles leave the domain; event ids), and nx=800 against the compiled
+    reference's fixture. Per case: teacher-forced steps of the N-rank handle vs a single-GPU handle (flags, counters
+    and event ids identical, fields <= 1e-10), three free-running steps, sharded transfers, ranks bit-identical.
+    Returns a compact block; `ok` False fails the run."""
+    had = os.environ.get("MPSB_MIN_SLAB_PARTICLES")
+    os.environ["MPSB_MIN_SLAB_PARTICLES"] = "0"  # shard the small cases too: this is about the sharded path
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import multi_gpu_check as M
+
+    rows, ok = [], True
+    try:
+        for what, steps in (("dambreak@200", 50), ("dambreak@320", 8), ("nx=800", 1)):
+            r = M.run_case(what, steps, rank, world, local)
+            good = bool(r["ok"])
+            if what == "dambreak@200":
+                good &= r["collisions_replayed"] > 0
+            if what == "dambreak@320":
+                good &= r["particles_ghosted"] > 0
+            if what.startswith("nx="):
+                good &= bool(r["vs_compiled_reference"] and r["vs_compiled_reference"]["ok"])
+            ok &= good
+            rows.append({"case": what, "steps": steps, "ok": good, "collisions": r["collisions_replayed"],
+                         "ghosted": r["particles_ghosted"], "ranks_bitwise": r["ranks_bit_identical"],
+                         "flags_counters_events": bool(r["flags_equal"] and r["counters_equal"] and r["event_ids_equal"]),
+                         "max_rel": max(r["max_rel_diff_vs_single_gpu"].values()),
+                         "free_run_max_rel": max(r["free_run_3_steps_max_rel_diff"].values()),
+                         "vs_reference_fixture": None if r["vs_compiled_reference"] is None else bool(r["vs_compiled_reference"]["ok"])})
+    finally:
+        if had is None:
+            os.environ.pop("MPSB_MIN_SLAB_PARTICLES", None)
+        else:
+            os.environ["MPSB_MIN_SLAB_PARTICLES"] = had
+    return {"ok": bool(ok), "tolerance": 1e-10, "cases": rows}
+
+
+def same_size_pair(nx, steps, cpu_point):
+    """The GPU on the very workload the CPU sample ran (same generator at nx, the same first `steps` steps from the
+    initial state, all host threads on the CPU side): device-resident and end to end through host buffers. One
+    apples-to-apples pair measured in this run on this box; the headline stays the full-size GPU line."""
+    import numpy as np
+    import torch
+
+    from mps_b200 import capi, cases as C
+
+    S, t, p, v = C.scaled_dambreak(nx)
+    stream = torch.cuda.current_stream()
+
+    def fresh():
+        d = capi.DeviceMPS(S, t, p, v)
+        d.set_stream(stream.cuda_stream)
+        d.load_initial_state()
+        return d
+
+    d = fresh()  # first use of this size: module / graph set-up outside the timed steps
+    for _ in range(3):
+        d.step_forward(False)
+    d.close()
+    d = fresh()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record(stream)
+    for _ in range(steps):
+        d.step_forward(False)
+    e1.record(stream)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    n = d.last_stats.n_active
+    d.close()
+    d = fresh()
+    st = d.download(["type", "position", "velocity", "pressure"])
+    pin = {k: torch.from_numpy(a).pin_memory() for k, a in st.items()}
+    host = {k: pin[k].numpy() for k in pin}
+    inputs = {k: host[k] for k in ("type", "position", "velocity")}
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        d.upload(inputs)
+        d.step_forward(False)
+        d.download_into(host)
+    torch.cuda.synchronize()
+    sec = time.perf_counter() - t0
+    d.close()
+    gpu_value, gpu_e2e = n * steps / (ms * 1e-3), n * steps / sec
+    return {"nx_fluid": nx, "particles": int(n), "steps": steps, "gpu_value": gpu_value, "gpu_e2e": gpu_e2e,
+            "gpu_ms_per_step": ms / steps, "cpu_value": cpu_point["value"], "cpu_threads": cpu_point["threads"],
+            "cpu_ms_per_step": cpu_point["ms_per_step"], "cpu_steps": cpu_point["steps"],
+            "ratio": gpu_value / cpu_point["value"], "e2e_ratio": gpu_e2e / cpu_point["value"], "unit": UNIT,
+            "how": "both sides: the first steps from the initial state of the same generated case; CPU = the compiled "
+                   "reference with all host threads (cpu_baseline.points), GPU = CUDA events / host clock around "
+                   "upload+step+download from pinned buffers"}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -410,6 +503,9 @@ def run_gpu_arm(args):
         if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
             os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    moving = None
+    if world > 1 and not args.no_parity:
+        moving = parity_in_motion(rank, world, local)  # its handles are closed again before the bench's own is made
     S, t, p, v = C.scaled_dambreak(args.nx)
     n_active0 = int(np.count_nonzero(t != C.GHOST))
     dev = capi.DeviceMPS(S, t, p, v, device=local)
@@ -497,7 +593,7 @@ def run_gpu_arm(args):
         pin = {k: torch.from_numpy(a).pin_memory() for k, a in st.items()}  # pinned host buffers
         host = {k: pin[k].numpy() for k in pin}
         inputs = {k: host[k] for k in ("type", "position", "velocity")}
-        n_e2e = max(1, min(args.steps, args.e2e_steps))
+        n_e2e = max(1, min(args.steps, args.e2e_steps if args.e2e_steps else args.steps))
         # several ranks: each rank moves only ITS block of particle ids over PCIe (mpsb_upload_shard /
         # mpsb_download_shard); the GPUs all-gather the uploaded blocks over NVLink. Bytes are per rank.
         shard = world > 1
@@ -533,6 +629,10 @@ def run_gpu_arm(args):
                "nx_fluid_timed": args.cpu_nx, "particles_timed": head["particles"], "points": pts,
                "full_size_measured_once": full_size_cpu_record(args.nx), "size_model": CPU_MODEL_TEXT}
 
+    same = None
+    if cpu is not None:
+        same = same_size_pair(args.cpu_nx, head["steps"], head)
+
     other = None
     if rank == 0 and world == 1 and not args.no_other:
         other = other_configs(args.other_steps, with_cpu=not args.no_cpu)
@@ -544,23 +644,25 @@ def run_gpu_arm(args):
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": workload_config(args.nx, len(t), "1 GPU" if world == 1 else f"{world} GPUs: every phase slab-decomposed by row blocks of the cell-major order "
                                       "(halo particles, migration, Krylov exchanges over NVLink peer memory)"),
+            # bulky blocks first, compact ones last: a reader of the tail of this line sees the numbers, not the prose
+            "other_configs": other, "cpu_baseline": cpu, "roofline": roofline,
             "ppe_solve_ms_per_step": mean("ms_solve"), "cg_iterations_per_step": mean("cg_iterations"),
-            "us_per_cg_iteration": 1e3 * solve_ms / max(1, sum(s["cg_iterations"] for s in stats)),
             "phase_ms_per_step": {k[3:]: mean(k) for k in ("ms_neighbors", "ms_explicit", "ms_collision", "ms_assemble",
                                                            "ms_solve", "ms_correct", "ms_total")},
             "n_inner": stats[-1]["n_inner"], "nnz": stats[-1]["nnz"],
-            "cg_cycle_split": {"A_spmv": cyc[0] / max(1, sum(cyc)), "B_update": cyc[1] / max(1, sum(cyc)),
-                               "C_direction": cyc[2] / max(1, sum(cyc)), "sync": cyc[3] / max(1, sum(cyc)),
-                               "of": "rank 0, CTA 0, last solve (SM cycles)"},
-            "sync_us_per_iteration": (cyc[3] / max(1, sum(cyc))) * 1e3 * solve_ms / max(1, sum(s["cg_iterations"] for s in stats)),
             "solve_options": {"recurrence": "single reduction (Chronopoulos-Gear, opt-in)" if stats[-1].get("cg_single_reduction") else
                               "textbook PCG = Eigen's loop (default)",
                               "matrix_free": bool(stats[-1].get("ppe_matrix_free")),
                               "l2_policy_of_matrix_stream": "evict_first + 16 MB evict_last for row blocks <= 2.5 M rows (multi-GPU splits); off at "
                                                             "4 M rows on one GPU" if os.environ.get("MPSB_L2_RESIDENT_KB") is None else
                                                             "MPSB_L2_RESIDENT_KB=" + os.environ["MPSB_L2_RESIDENT_KB"]},
-            "parity_vs_1gpu": parity, "other_configs": other,
-            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+            "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "same_size": same,
+            "parity_vs_1gpu": parity, "parity_in_motion": moving,
+            "cg_cycle_split": {"A_spmv": cyc[0] / max(1, sum(cyc)), "B_update": cyc[1] / max(1, sum(cyc)),
+                               "C_direction": cyc[2] / max(1, sum(cyc)), "sync": cyc[3] / max(1, sum(cyc)),
+                               "of": "rank 0, CTA 0, last solve (SM cycles)"},
+            "sync_us_per_iteration": (cyc[3] / max(1, sum(cyc))) * 1e3 * solve_ms / max(1, sum(s["cg_iterations"] for s in stats)),
+            "us_per_cg_iteration": 1e3 * solve_ms / max(1, sum(s["cg_iterations"] for s in stats)),
         }
         _emit(out)
     dev.close()
@@ -568,6 +670,9 @@ def run_gpu_arm(args):
         torch.distributed.destroy_process_group()
     if parity is not None and not parity["ok"]:
         sys.stderr.write("bench.py: N-GPU result differs from one GPU beyond 1e-10: %s\n" % json.dumps(parity))
+        return 3
+    if moving is not None and not moving["ok"]:
+        sys.stderr.write("bench.py: the slab path in motion missed its bars: %s\n" % json.dumps(moving))
         return 3
     return 0
 
@@ -605,7 +710,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--nx", type=int, default=DEFAULT_NX, help="fluid columns of the scaled dam break (multiple of 8)")
     ap.add_argument("--cpu-nx", type=int, default=CPU_SAMPLE_NX, help="size of the bounded CPU sample")
-    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--e2e-steps", type=int, default=0, help="steps of the end-to-end leg (0 = as many as --steps)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-other", action="store_true", help="skip the other_configs block (BASELINE configs 0, 1, 2, 4)")

@@ -20,17 +20,14 @@ os.environ.setdefault("MPSB_MIN_SLAB_PARTICLES", "0")  # this check is about the
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 
-def main():
+def run_case(what, steps, rank, world, local):
+    """One case on an already initialised NCCL process group (this rank's device current). Returns the report
+    (the same dict on every rank; `ok` is the minimum over the ranks). bench.py calls this at N > 1 as well."""
     import torch
     import torch.distributed as dist
 
     from mps_b200 import capi, cases as C
 
-    what = sys.argv[1] if len(sys.argv) > 1 else "dambreak"
-    steps = int(sys.argv[2]) if len(sys.argv) > 2 else 5
-    rank, world, local = (int(os.environ[k]) for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"))
-    torch.cuda.set_device(local)
-    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     prerun = 0
     if "@" in what:  # "dambreak@200": the 1-GPU handle first runs 200 steps, so collisions / ghost events are live
         what, prerun = what.split("@")[0], int(what.split("@")[1])
@@ -131,16 +128,30 @@ def main():
         all(x <= 1e-8 for x in free.values()) and (vs_reference is None or vs_reference["ok"])
     okt = torch.tensor([int(ok)], device="cuda")
     dist.all_reduce(okt, op=dist.ReduceOp.MIN)
-    if rank == 0:
-        print(json.dumps({"case": what, "world": world, "steps": steps, "ranks_bit_identical": bool(same.item()),
-                          "flags_equal": flags_equal, "counters_equal": counters_equal, "event_ids_equal": events_equal, "matrix_free_on_multi": int(matrix_free_multi), "sharded_transfers_ok": bool(shard_ok), "max_rel_diff_vs_single_gpu": worst,
-                          "free_run_3_steps_max_rel_diff": free, "vs_compiled_reference": vs_reference,
-                          "collisions_replayed": collisions, "particles_ghosted": ghosted,
-                          "cg_iterations_multi_vs_single": iters[-3:], "ok": bool(okt.item())}), flush=True)
     multi.close()
     single.close()
+    return {"case": what + (f"@{prerun}" if prerun else ""), "world": world, "steps": steps, "ranks_bit_identical": bool(same.item()),
+            "flags_equal": flags_equal, "counters_equal": counters_equal, "event_ids_equal": events_equal,
+            "matrix_free_on_multi": int(matrix_free_multi), "sharded_transfers_ok": bool(shard_ok),
+            "max_rel_diff_vs_single_gpu": worst, "free_run_3_steps_max_rel_diff": free, "vs_compiled_reference": vs_reference,
+            "collisions_replayed": collisions, "particles_ghosted": ghosted,
+            "cg_iterations_multi_vs_single": iters[-3:], "ok": bool(okt.item())}
+
+
+def main():
+    import torch
+    import torch.distributed as dist
+
+    what = sys.argv[1] if len(sys.argv) > 1 else "dambreak"
+    steps = int(sys.argv[2]) if len(sys.argv) > 2 else 5
+    rank, world, local = (int(os.environ[k]) for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"))
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    rep = run_case(what, steps, rank, world, local)
+    if rank == 0:
+        print(json.dumps(rep), flush=True)
     dist.destroy_process_group()
-    return 0 if okt.item() else 1
+    return 0 if rep["ok"] else 1
 
 
 if __name__ == "__main__":
