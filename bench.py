@@ -310,11 +310,26 @@ def other_configs(gpu_steps, with_cpu=True, cpu_seconds=1.5):
             row["cpu_threads_all"] = cpu_threads()
             row["speedup_vs_best_cpu"] = min(row["cpu_ms_per_step_1_thread"], row["cpu_ms_per_step_all_threads"]) / row["gpu_ms_per_step"]
         rows.append(row)
-    # a 3-D case at a size where bandwidth starts to matter (the reference ships none): the generated
-    # open tank of tests/golden/tank3d_*, 4x finer (radius ratio 2.1 -> ~120 neighbours, K = 384 slots)
+    # 3-D cases at sizes where bandwidth starts to matter (the reference ships none): the generated open
+    # tank of tests/golden/tank3d_*, 4x finer, at radius ratio 2.1 (~37 neighbours) and at the ratio every settings.yml
+    # of the reference ships, 3.1 (~120 neighbours, K = 384 slots, ~1.2 kB of PPE row per particle)
+    for ratio, n_fluid, n_tank in ((2.1, (32, 40, 24), (64, 56, 24)), (3.1, (64, 64, 40), (128, 80, 40))):
+        try:
+            rows.append(tank3d_row(ratio, n_fluid, n_tank, gpu_steps, with_cpu and ratio == 2.1, cpu_seconds))
+        except Exception as e:  # a row of context must not take the headline line down with it
+            rows.append({"config": "3-D (SURVEY 8 f-4, generated)", "radius_ratio": ratio, "error": str(e)[:300]})
+    return rows
+
+
+def tank3d_row(ratio, n_fluid, n_tank, gpu_steps, with_cpu, cpu_seconds):
     import tempfile
 
-    S, t, p, v = C.tank3d(n_fluid=(32, 40, 24), n_tank=(64, 56, 24), jitter=0.05)
+    import numpy as np
+
+    from mps_b200 import capi, cases as C
+    from oracle import refbind as R
+
+    S, t, p, v = C.tank3d(n_fluid=n_fluid, n_tank=n_tank, ratio=ratio, jitter=0.05)
     n = int(np.count_nonzero(t != C.GHOST))
     dev = capi.DeviceMPS(S, t, p, v)
     dev.load_initial_state()
@@ -330,11 +345,18 @@ def other_configs(gpu_steps, with_cpu=True, cpu_seconds=1.5):
         solve.append(st.ms_solve)
         tot.append(st.ms_total)
     wall = time.perf_counter() - t0
-    row = {"config": "3-D (SURVEY 8 f-4, generated)", "case": "tank3d 64x56x24 cells, fluid 32x40x24", "particles": n,
+    st = dev.last_stats
+    it_all, solve_ms = max(1, int(np.sum(its))), float(np.sum(solve))
+    bytes_it = 12.0 * st.nnz + 108.0 * st.n_inner  # algorithmic bytes per CG iteration
+    row = {"config": "3-D (SURVEY 8 f-4, generated)", "radius_ratio": ratio,
+           "case": "tank3d %dx%dx%d cells, fluid %dx%dx%d" % (n_tank + n_fluid), "particles": n,
            "gpu_steps": steps3, "gpu_ms_per_step": 1e3 * wall / steps3, "gpu_particle_steps_per_s": n * steps3 / wall,
            "gpu_solve_ms_per_step": float(np.mean(solve)), "cg_iterations_per_step": float(np.mean(its)),
-           "gpu_us_per_cg_iteration": 1e3 * float(np.sum(solve)) / max(1, int(np.sum(its))),
-           "max_neighbors": int(dev.last_stats.max_neighbors), "nnz": int(dev.last_stats.nnz)}
+           "gpu_us_per_cg_iteration": 1e3 * solve_ms / it_all,
+           "max_neighbors": int(st.max_neighbors), "nnz": int(st.nnz), "n_inner": int(st.n_inner),
+           "algorithmic_bytes_per_cg_iteration": bytes_it,
+           "solve_algorithmic_gbs": bytes_it * it_all / (solve_ms * 1e-3) / 1e9 if solve_ms > 0 else None,
+           "solve_in_cluster": int(st.solve_in_cluster), "ppe_columns_16bit": int(st.ppe_columns_16bit)}
     dev.close()
     if with_cpu and R.have_ref():
         yml = C.write_settings_yaml(S, os.path.join(tempfile.mkdtemp(prefix="mpsb_bench3d_"), "settings.yml"))
@@ -349,8 +371,8 @@ def other_configs(gpu_steps, with_cpu=True, cpu_seconds=1.5):
         row["cpu_threads_all"] = cpu_threads()
         row["speedup_vs_best_cpu"] = row["cpu_ms_per_step_all_threads"] / row["gpu_ms_per_step"]
         ref.close()
-    rows.append(row)
-    return rows
+    return row
+
 
 
 def parity_vs_one_gpu(dev, S, t, p, v, local, world):

@@ -278,9 +278,11 @@ def case_paths(name: str):
 
 
 def load_case(name: str):
-    """(Settings, type, pos, vel) of a shipped case under cases/<name>/ (or the generated 3-D case "tank3d")."""
+    """(Settings, type, pos, vel) of a shipped case under cases/<name>/ (or the generated 3-D cases "tank3d" / "tank3d_r31")."""
     if name == "tank3d":
         return tank3d(jitter=0.05)
+    if name == "tank3d_r31":  # the radius ratio every settings.yml of the reference ships (tutorials/dambreak/settings.yml:27-30): ~120 neighbours in 3-D
+        return tank3d(ratio=3.1, jitter=0.05)
     yml, _ = case_paths(name)
     s = load_settings(yml)
     csv = s.input_csv_path if os.path.isabs(s.input_csv_path) else os.path.join(REPO_ROOT, s.input_csv_path)

@@ -25,6 +25,7 @@ PLAN = {
     "dambreak_fine_original": [0, 20],
     "dambreak_fine_higher_order": [0, 20],
     "tank3d": [0, 5],                              # generated 3-D case (mps_b200.cases.tank3d); the reference ships none
+    "tank3d_r31": [0, 5],                          # the same tank at the reference's shipped radius ratio 3.1 (~120 neighbours per particle)
 }
 
 
@@ -39,7 +40,7 @@ def main():
     for case, steps in PLAN.items():
         if only and case not in only:
             continue
-        if case == "tank3d":
+        if case.startswith("tank3d"):
             import tempfile
 
             S, t, p, v = C.load_case(case)

@@ -43,10 +43,10 @@ def test_oracle_ppe_and_cg_match_golden(path):
 
 @pytest.mark.skipif(not R.have_ref(), reason="oracle/_ref not built (needs /root/reference)")
 @pytest.mark.parametrize("case,steps", [("dambreak", 120), ("hydrostatic", 6), ("dambreak_fine_higher_order", 4),
-                                        ("tank3d", 6)])
+                                        ("tank3d", 6), ("tank3d_r31", 3)])
 def test_oracle_free_run_matches_compiled_reference(case, steps, tmp_path):
     S, t, p, v = C.load_case(case)
-    if case == "tank3d":  # generated 3-D case: the reference takes its settings from a YAML written for it
+    if case.startswith("tank3d"):  # generated 3-D case: the reference takes its settings from a YAML written for it
         ref = R.RefMPS(C.write_settings_yaml(S, str(tmp_path / "settings.yml")), arrays=(t, p, v))
     else:
         yml, _ = C.case_paths(case)
